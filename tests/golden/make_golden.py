@@ -1,0 +1,182 @@
+"""Generate golden vectors by running the UNMODIFIED reference (imported from /root/reference) on CPU.
+
+Run in the build container only:  python tests/golden/make_golden.py
+Writes tests/golden/*.npz.  bf16/fp16 tensors are stored as float32 (exact) plus a dtype tag; the
+reference has no golden vectors of its own, so these are the parity pin for oracle/.
+"""
+import os
+import sys
+import types
+
+import numpy as np
+import torch
+
+REF = "/root/reference/quantization"
+OUT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, REF)
+sys.modules.setdefault("awq_inference_engine", types.ModuleType("awq_inference_engine"))
+
+import quantizer as rq  # noqa: E402
+
+DT = {"f32": torch.float32, "bf16": torch.bfloat16, "f16": torch.float16}
+
+
+def f32(t):
+    return t.detach().to(torch.float32).numpy()
+
+
+def make_inputs(kind, rows, cols, dtype, seed):
+    g = torch.Generator().manual_seed(seed)
+    if kind == "randn":
+        w = torch.randn(rows, cols, generator=g) * 0.02
+    elif kind == "uniform":
+        w = torch.rand(rows, cols, generator=g) - 0.5
+    elif kind == "heavy":
+        w = torch.randn(rows, cols, generator=g) ** 3 * 0.02
+    elif kind == "pos":  # groups that do not straddle zero -> z clamps, mask has zeros
+        w = torch.rand(rows, cols, generator=g) * 0.1 + 0.3
+        w[rows // 2:] = -w[rows // 2:]
+    elif kind == "edge":  # constant groups, all-zero groups, tiny ranges, ties
+        w = torch.randn(rows, cols, generator=g) * 0.02
+        w[0] = 0.0
+        w[1] = 0.0123
+        w[2] = w[2] * 1e-5
+        w[3] = torch.round(w[3] * 200) / 200  # many ties
+        w[4, :] = w[4, :].abs()  # min >= 0
+        w[5, :] = -w[5, :].abs()
+    else:
+        raise ValueError(kind)
+    return w.to(dtype)
+
+
+def gen_pq_int():
+    out = {}
+    idx = 0
+    for dname, dtype in DT.items():
+        for kind in ["randn", "uniform", "heavy", "pos", "edge"]:
+            for n_bit, G in [(2, 128), (2, 64), (3, 128), (4, 128), (8, 128), (2, -1), (4, 32)]:
+                w = make_inputs(kind, 8, 256, dtype, 100 + idx)
+                dq, s, z = rq.pseudo_quantize_tensor(w.clone(), n_bit=n_bit, zero_point=True, q_group_size=G,
+                                                     get_scale_zp=True)
+                dq2 = rq.pseudo_quantize_tensor(w.clone(), n_bit=n_bit, zero_point=True, q_group_size=G, inplace=True)
+                assert torch.equal(dq, dq2.reshape(dq.shape))
+                k = f"c{idx}"
+                out[k + "_meta"] = np.array([dname, kind, str(n_bit), str(G)])
+                out[k + "_w"], out[k + "_dq"], out[k + "_s"], out[k + "_z"] = f32(w), f32(dq), f32(s), f32(z)
+                idx += 1
+    np.savez_compressed(os.path.join(OUT, "pq_int.npz"), **out)
+    print("pq_int", idx)
+
+
+def gen_ste():
+    out = {}
+    idx = 0
+    for qname in ["int2", "int3", "nf3"]:
+        for dname, dtype in DT.items():
+            for kind in ["randn", "heavy", "uniform", "ties", "pos"]:
+                for G in [64, 128]:
+                    if kind == "ties":
+                        w = make_inputs("randn", 8, 256, torch.float32, 300 + idx)
+                        lim = w.reshape(8, -1, G).abs().amax(-1, keepdim=True) * 0.7  # emulate apply_clip ties
+                        w = torch.clamp(w.reshape(8, -1, G), -lim, lim).reshape(8, 256).to(dtype)
+                    else:
+                        w = make_inputs(kind, 8, 256, dtype, 300 + idx)
+                    if qname == "nf3" and kind == "pos":
+                        pass  # all-positive / all-negative groups are fine for nf3
+                    gy = torch.randn(8, 256, generator=torch.Generator().manual_seed(900 + idx)).to(dtype)
+                    mk = {"int2": lambda: rq.SteInt2AsymQuantizer(G), "int3": lambda: rq.SteInt3AsymQuantizer(G),
+                          "nf3": lambda: rq.SteN2F3Quantizer(G)}[qname]
+                    res = {}
+                    for pname, pd in [("T", dtype), ("f64", torch.float64)]:
+                        x = w.to(pd).clone().requires_grad_(True)
+                        y = mk()(x)
+                        y.backward(gy.to(pd))
+                        res[pname] = (y.detach(), x.grad.detach())
+                    k = f"c{idx}"
+                    out[k + "_meta"] = np.array([qname, dname, kind, str(G)])
+                    out[k + "_w"], out[k + "_gy"] = f32(w), f32(gy)
+                    out[k + "_y"], out[k + "_gw"] = f32(res["T"][0]), f32(res["T"][1])
+                    out[k + "_gw64"] = res["f64"][1].numpy()
+                    idx += 1
+    # NaN behaviour of nf3 (min exactly 0 in a group)
+    w = make_inputs("randn", 2, 256, torch.bfloat16, 77)
+    w[0, :128] = w[0, :128].abs()
+    w[0, 5] = 0.0
+    y = rq.pseudo_quantize_n2f3_tensor(w, 128)
+    out["nan_w"], out["nan_y"] = f32(w), f32(y)
+    np.savez_compressed(os.path.join(OUT, "ste.npz"), **out)
+    print("ste", idx)
+
+
+def gen_clip_autoclip():
+    import autoclip as ra  # pulls transformers/datasets (slow import)
+    from clip_utils import apply_clip
+
+    out = {}
+    idx = 0
+    for dname in ["f32", "bf16"]:
+        dtype = DT[dname]
+        for qt in ["int", "nf3"]:
+            for G, co, ci, ntok in [(128, 64, 256, 512), (64, 64, 128, 1100)]:
+                g = torch.Generator().manual_seed(500 + idx)
+                w = (torch.randn(co, ci, generator=g) * 0.02).to(dtype)
+                ch = torch.exp(torch.randn(ci, generator=g) * 0.5)
+                x = (torch.randn(ntok, ci, generator=g) * ch).to(dtype)
+                q_config = {"zero_point": True, "q_group_size": G, "quant_type": qt}
+                bmax, bmin = ra.auto_2clip_layer(w.clone(), x.clone(), n_bit=2, q_config=q_config)
+                k = f"c{idx}"
+                out[k + "_meta"] = np.array([dname, qt, str(G)])
+                out[k + "_w"], out[k + "_x"] = f32(w), f32(x)
+                out[k + "_bmax"], out[k + "_bmin"] = f32(bmax), f32(bmin)
+                # apply_clip on a module holding this weight
+                lin = torch.nn.Linear(ci, co, bias=False, dtype=dtype)
+                lin.weight.data = w.clone()
+                holder = torch.nn.Module()
+                holder.proj = lin
+                torch.nn.Module.cuda = lambda self, *a, **k: self  # the reference calls layer.cuda(); no GPU here
+                apply_clip(holder, [("proj", bmax, bmin)])
+                out[k + "_wclip"] = f32(holder.proj.weight.data)
+                idx += 1
+    np.savez_compressed(os.path.join(OUT, "autoclip.npz"), **out)
+    print("autoclip", idx)
+
+
+def gen_pack():
+    import qmodule as rm
+
+    out = {}
+    idx = 0
+    for dname in ["f16", "f32", "bf16"]:
+        dtype = DT[dname]
+        for w_bit, G, rows, cols in [(2, 128, 32, 256), (2, 128, 16, 384), (2, 64, 16, 256), (4, 128, 16, 256),
+                                     (2, 128, 16, 2304), (4, 64, 8, 128)]:
+            g = torch.Generator().manual_seed(700 + idx)
+            lin = torch.nn.Linear(cols, rows, bias=(idx % 2 == 0), dtype=dtype)
+            lin.weight.data = (torch.randn(rows, cols, generator=g) * 0.02).to(dtype)
+            w0 = lin.weight.data.clone()
+            dq, s, z = rq.pseudo_quantize_tensor(lin.weight.data, n_bit=w_bit, zero_point=True, q_group_size=G,
+                                                 get_scale_zp=True)
+            lin.weight.data = dq
+            ql = rm.WQLinear.from_linear(lin, w_bit, G, False, s, z)
+            k = f"c{idx}"
+            out[k + "_meta"] = np.array([dname, str(w_bit), str(G)])
+            out[k + "_w"], out[k + "_dq"], out[k + "_s"], out[k + "_z"] = f32(w0), f32(dq), f32(s), f32(z)
+            out[k + "_qweight"] = ql.qweight.numpy()
+            out[k + "_qzeros"] = ql.qzeros.numpy()
+            out[k + "_qscales"] = f32(ql.scales)
+            idx += 1
+    np.savez_compressed(os.path.join(OUT, "pack.npz"), **out)
+    print("pack", idx)
+
+
+if __name__ == "__main__":
+    torch.manual_seed(0)
+    which = sys.argv[1:] or ["pq", "ste", "pack", "clip"]
+    if "pq" in which:
+        gen_pq_int()
+    if "ste" in which:
+        gen_ste()
+    if "pack" in which:
+        gen_pack()
+    if "clip" in which:
+        gen_clip_autoclip()
