@@ -1,0 +1,95 @@
+/*
+ * bdq.h -- C ABI of libbdq.so: B200 (sm_100a) kernels for BitDistiller's low-bit weight-quantisation hot path.
+ *
+ * Every entry point replaces one function of the reference (file:line under the reference tree cited per
+ * function).  Conventions:
+ *   - plain pointers and sizes only; all tensor pointers are DEVICE pointers unless the name ends in _host;
+ *   - the caller owns every buffer, the library never allocates device memory except inside *_host entries;
+ *   - `stream` is a cudaStream_t passed as void*; entries are asynchronous, re-entrant and graph-capturable;
+ *   - return value: BDQ_OK or a negative BDQ_ERR_* code; bdq_last_error() gives a thread-local message;
+ *   - dtype: BDQ_F32 / BDQ_BF16 / BDQ_F16 = logical dtype T of the weight tensors.  Arithmetic reproduces
+ *     eager PyTorch op by op (every intermediate rounded to T);
+ *   - sem: BDQ_SEM_CPU reproduces CPU-eager rounding (true division by the python scalar), BDQ_SEM_CUDA
+ *     reproduces CUDA-eager (multiply by the fp32 reciprocal of the scalar)  -- SURVEY.md App. D-1.
+ */
+#ifndef BDQ_H_
+#define BDQ_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BDQ_F32 0
+#define BDQ_BF16 1
+#define BDQ_F16 2
+
+#define BDQ_SEM_CPU 0
+#define BDQ_SEM_CUDA 1
+
+#define BDQ_ROUND_HALF_EVEN 0 /* torch.round: pseudo_quantize_tensor, quantizer.py:60 */
+#define BDQ_ROUND_HALF_AWAY 1 /* Round.apply: Ste*AsymQuantizer, quantizer.py:12-17,176 */
+
+#define BDQ_QUANT_INT 0 /* q_config["quant_type"] == "int", autoclip.py:55 */
+#define BDQ_QUANT_NF3 1 /* q_config["quant_type"] == "nf3", autoclip.py:57 */
+
+#define BDQ_OK 0
+#define BDQ_ERR_SHAPE (-1)
+#define BDQ_ERR_DTYPE (-2)
+#define BDQ_ERR_ALIGN (-3)
+#define BDQ_ERR_CUDA (-4)
+#define BDQ_ERR_UNSUPPORTED (-5)
+
+typedef void* bdq_stream_t;
+
+int bdq_version(void);
+const char* bdq_last_error(void);
+
+/* Kernels launched by this library since load (monotonic; bench.py reports the delta as gpu_launches). */
+int64_t bdq_launch_count(void);
+
+/*
+ * Group asymmetric integer fake-quant, one fused pass.
+ * Replaces pseudo_quantize_tensor (quantization/quantizer.py:25-69; round_mode HALF_EVEN) and the forward of
+ * SteInt2AsymQuantizer / SteInt3AsymQuantizer (quantizer.py:119-182; round_mode HALF_AWAY).
+ * w, dq: n_elem values of dtype T (dq may alias w = the inplace=True path, quantizer.py:56-58).
+ * group: q_group_size (> 0, divides the innermost dimension; the caller resolves -1 to the row length).
+ * Optional outputs (NULL to skip): scales, zeros [n_elem/group] of dtype T (get_scale_zp, quantizer.py:66-67),
+ * codes [n_elem] uint8.  Optional clip_min/clip_max [n_elem/group] of dtype T: clamp first, i.e. apply_clip
+ * (quantization/clip_utils.py:343-345) fused in front.
+ */
+int bdq_int_fakequant_fwd(const void* w, void* dq, void* scales, void* zeros, uint8_t* codes,
+                          const void* clip_min, const void* clip_max, int64_t n_elem, int group, int bits,
+                          int dtype, int round_mode, int sem, bdq_stream_t stream);
+
+/*
+ * Straight-through backward of Ste{Int2,Int3}AsymQuantizer = autograd over quantizer.py:166-177 in one pass:
+ * gw = gy*mask + d(scale)/d(amax,amin) terms with even tie splitting.  Recomputes the
+ * forward from w; nothing is saved.  fp32 internal accumulation.  gw may alias gy.
+ */
+int bdq_int_ste_bwd(const void* w, const void* gy, void* gw, int64_t n_elem, int group, int bits, int dtype,
+                    int sem, bdq_stream_t stream);
+
+/*
+ * NF3 (8-level, two scales per group) fake-quant.  Replaces SteN2F3Quantizer.forward
+ * (quantization/quantizer.py:189-242) and pseudo_quantize_n2f3_tensor (quantizer.py:113-116).
+ * Optional: codes [n_elem] uint8 (0..4 positive level, 5..7 negative level 1..3, 255 NaN),
+ * scale_pos/scale_neg [n_elem/group] (T), clip_min/clip_max as above.
+ */
+int bdq_nf3_fakequant_fwd(const void* w, void* dq, void* scale_pos, void* scale_neg, uint8_t* codes,
+                          const void* clip_min, const void* clip_max, int64_t n_elem, int group, int dtype,
+                          int sem, bdq_stream_t stream);
+
+/* Backward of SteN2F3Quantizer (identity + scale terms through amax/amin). */
+int bdq_nf3_ste_bwd(const void* w, const void* gy, void* gw, int64_t n_elem, int group, int dtype, int sem,
+                    bdq_stream_t stream);
+
+/* apply_clip (quantization/clip_utils.py:328-346): w = clamp(w, clip_min[g], clip_max[g]) in place. */
+int bdq_apply_clip(void* w, const void* clip_min, const void* clip_max, int64_t n_elem, int group, int dtype,
+                   bdq_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BDQ_H_ */

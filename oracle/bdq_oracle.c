@@ -12,8 +12,9 @@
  * Conventions: tensors travel as float32 arrays whose values are representable in the logical
  * dtype T (0 = fp32, 1 = bf16, 2 = fp16); rT() rounds an fp32 opmath result to T exactly like a
  * PyTorch eager op does between two kernels.  `sem` selects eager-device semantics:
- *   0 = CPU eager  (tensor / python_scalar is a true division; bf16 scalar compares cast the scalar to T)
- *   1 = CUDA eager (tensor / python_scalar multiplies by the fp32 reciprocal; compares run in fp32)
+ *   0 = CPU eager  (tensor / python_scalar is a true division)
+ *   1 = CUDA eager (tensor / python_scalar multiplies by the fp32 reciprocal)
+ * (scalar compares cast the python scalar to T on BOTH devices -- measured, tools/dbg_nf3.py)
  * All citations are file:line under /root/reference.
  */
 #include <math.h>
@@ -151,8 +152,8 @@ static const double NF3_NEG_LVL[4] = {0.0, -0.2469314038753510, -0.5350227355957
 static const double NF3_NEG_THR[3] = {-0.1234657019376755, -0.39097706973552704, -0.7675113677978516};
 
 static inline float thrT(double t, int dt, int sem) {
-    float f = (float)t;
-    return sem == 0 ? rT(f, dt) : f; /* CPU eager casts the wrapped scalar to T; CUDA eager compares in fp32 */
+    (void)sem; /* measured on B200: CUDA eager, like CPU eager, casts the wrapped python scalar to T */
+    return rT((float)t, dt);
 }
 
 /* returns level index 0..4 (NaN -> -1: every where() leaves q untouched) */

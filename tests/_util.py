@@ -35,3 +35,54 @@ def ulp_of(x, dtype):
     tiny = {torch.float32: -126, torch.bfloat16: -126, torch.float16: -14}[dtype]
     e = torch.floor(torch.log2(torch.clamp(x, min=2.0 ** tiny)))
     return torch.pow(torch.tensor(2.0, dtype=torch.float64), e - mant)
+
+
+# ---- plain eager-PyTorch restatements (run on whatever device the input lives on; used to confirm the
+# ---- CPU-eager vs CUDA-eager rounding hypothesis of SURVEY.md App. D on the GPU box)
+def torch_int_fakequant(w, n_bit, G, half_away):
+    shp = w.shape
+    x = w.reshape(-1, G)
+    mx, mn = x.amax(1, keepdim=True), x.amin(1, keepdim=True)
+    qmax = 2 ** n_bit - 1
+    s = (mx - mn).clamp(min=1e-5) / qmax
+    z = (-torch.round(mn / s)).clamp_(0, qmax)
+    u = x / s
+    r = torch.sign(u) * torch.floor(torch.abs(u) + 0.5) if half_away else torch.round(u)
+    dq = (torch.clamp(r + z, 0, qmax) - z) * s
+    return dq.reshape(shp), s.reshape(shp[0], -1), z.reshape(shp[0], -1)
+
+
+def torch_nf3_fakequant(w, G):
+    shp = w.shape
+    x = w.reshape(-1, G)
+    sp, sn = x.amax(1, keepdim=True).abs(), x.amin(1, keepdim=True).abs()
+    zero = torch.zeros_like(x)
+    qp = torch.where(x >= 0, x, zero) / sp
+    qn = torch.where(x < 0, x, zero) / sn
+    dev = x.device
+    T = lambda v: torch.tensor(v).to(dev)
+    yp = torch.where(qp >= 0.8114928305149078, T(1.0), qp)
+    yp = torch.where((yp < 0.8114928305149078) & (yp >= 0.5024898052215576), T(0.6229856610298157), yp)
+    yp = torch.where((yp < 0.5024898052215576) & (yp >= 0.2826657369732857), T(0.3819939494132996), yp)
+    yp = torch.where((yp < 0.2826657369732857) & (yp >= 0.0916687622666359), T(0.1833375245332718), yp)
+    yp = torch.where(yp < 0.0916687622666359, T(0), yp)
+    yn = torch.where(qn >= -0.1234657019376755, T(0), qn)
+    yn = torch.where((yn < -0.1234657019376755) & (yn >= -0.39097706973552704), T(-0.2469314038753510), yn)
+    yn = torch.where((yn < -0.39097706973552704) & (yn >= -0.7675113677978516), T(-0.5350227355957031), yn)
+    yn = torch.where(yn < -0.7675113677978516, T(-1.0), yn)
+    yp = (yp - qp) + qp
+    yn = (yn - qn) + qn
+    return (yp * sp + yn * sn).reshape(shp)
+
+
+def make_weight(kind, rows, cols, dtype, seed):
+    g = torch.Generator().manual_seed(seed)
+    if kind == "randn":
+        w = torch.randn(rows, cols, generator=g) * 0.02
+    elif kind == "uniform":
+        w = torch.rand(rows, cols, generator=g) - 0.5
+    elif kind == "heavy":
+        w = torch.randn(rows, cols, generator=g) ** 3 * 0.02
+    else:
+        raise ValueError(kind)
+    return w.to(dtype)

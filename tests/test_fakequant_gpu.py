@@ -1,0 +1,187 @@
+"""GPU parity tests for the fused fake-quant / STE kernels (through the C ABI via bitdistiller_b200.quantizer).
+
+Bars (BASELINE.json north_star): codes, zeros, scales bit-exact; dequantised weights bit-exact here (the stated
+bar is <= 1 bf16 ulp); backward within the reference's own T-dtype autograd noise of the float64 closed form.
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from _util import (DT, GOLDEN, bits_equal, load_cases, make_weight, t, torch_int_fakequant, torch_nf3_fakequant,
+                   ulp_of)
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(autouse=True)
+def _cpu_semantics(monkeypatch):
+    monkeypatch.setenv("BDQ_SEMANTICS", "cpu")
+
+
+def dev():
+    return torch.device("cuda:0")
+
+
+def test_pseudo_quantize_tensor_golden_bit_exact():
+    from bitdistiller_b200.quantizer import pseudo_quantize_tensor
+    n = 0
+    for meta, c in load_cases("pq_int"):
+        dname, kind, n_bit, G = meta[0], meta[1], int(meta[2]), int(meta[3])
+        dt = DT[dname]
+        w = t(c["w"], dt).to(dev())
+        dq, s, z = pseudo_quantize_tensor(w, n_bit=n_bit, zero_point=True, q_group_size=G, get_scale_zp=True)
+        assert dq.dtype == dt and dq.shape == w.shape
+        assert bits_equal(dq.cpu(), t(c["dq"], dt)), meta
+        assert bits_equal(s.cpu(), t(c["s"], dt)), meta
+        assert bits_equal(z.cpu(), t(c["z"], dt)), meta
+        w2 = w.clone()
+        r = pseudo_quantize_tensor(w2, n_bit=n_bit, zero_point=True, q_group_size=G, inplace=True)
+        assert bits_equal(w2.cpu(), t(c["dq"], dt)) and r.data_ptr() == w2.data_ptr(), meta
+        n += 1
+    assert n == 105
+
+
+def _bwd_check(gw, w, gy, G, ref64, dt, meta):
+    """|ours - closed form(double)| bounded by the rounding of the output dtype plus fp32 accumulation noise."""
+    gw = gw.double().cpu()
+    tol = 1.01 * ulp_of(ref64, dt) + 1e-30
+    gsum = gy.double().abs().reshape(-1, G).sum(1, keepdim=True).expand(-1, G).reshape(ref64.shape)
+    tol = tol + 1e-5 * gsum
+    bad = (gw - ref64).abs() > tol
+    assert not bool(bad.any()), (meta, int(bad.sum()), float((gw - ref64).abs().max()))
+
+
+def test_ste_quantizers_golden():
+    from bitdistiller_b200.quantizer import SteInt2AsymQuantizer, SteInt3AsymQuantizer, SteN2F3Quantizer
+    n = 0
+    for meta, c in load_cases("ste"):
+        qname, dname, kind, G = meta[0], meta[1], meta[2], int(meta[3])
+        dt = DT[dname]
+        w, gy = t(c["w"], dt), t(c["gy"], dt)
+        mod = {"int2": SteInt2AsymQuantizer, "int3": SteInt3AsymQuantizer, "nf3": SteN2F3Quantizer}[qname](G)
+        x = w.to(dev()).requires_grad_(True)
+        y = mod(x)
+        y.backward(gy.to(dev()))
+        assert bits_equal(y.detach().cpu(), t(c["y"], dt)), meta
+        if qname == "nf3":
+            ref64 = oracle.nf3_ste_bwd(w, gy, G)
+        else:
+            ref64 = oracle.int_ste_bwd(w, gy, G, int(qname[-1]))
+        _bwd_check(x.grad, w, gy, G, ref64, dt, meta)
+        n += 1
+    assert n == 90
+    z = np.load(os.path.join(GOLDEN, "ste.npz"))
+    from bitdistiller_b200.quantizer import pseudo_quantize_n2f3_tensor
+    y = pseudo_quantize_n2f3_tensor(t(z["nan_w"], torch.bfloat16).to(dev()), 128)
+    assert bits_equal(y.cpu(), t(z["nan_y"], torch.bfloat16))
+
+
+@pytest.mark.parametrize("dname", ["f32", "bf16", "f16"])
+@pytest.mark.parametrize("kind", ["randn", "uniform", "heavy"])
+def test_large_vs_oracle(dname, kind):
+    """[512, 4096] per dtype: codes / scales / zeros / dq bit-exact against the oracle, both rounding modes, + NF3."""
+    from bitdistiller_b200 import quantizer as Q
+    dt = DT[dname]
+    w = make_weight(kind, 512, 4096, dt, 1234)
+    wd = w.to(dev())
+    for bits, G, rm in [(2, 128, 0), (2, 128, 1), (2, 64, 1), (3, 128, 1), (4, 32, 0), (2, 4096, 0)]:
+        ref = oracle.int_fakequant(w, G, bits, round_mode=rm)
+        dq, s, z, codes = Q.int_fakequant(wd, bits, G, rm, want_scale_zp=True, want_codes=True)
+        assert bits_equal(dq.cpu(), ref["dq"]), (bits, G, rm)
+        assert bits_equal(s.cpu().reshape(ref["scales"].shape), ref["scales"])
+        assert bits_equal(z.cpu().reshape(ref["zeros"].shape), ref["zeros"])
+        assert torch.equal(codes.cpu(), ref["codes"])
+    for G in [128, 64]:
+        ref = oracle.nf3_fakequant(w, G)
+        dq, sp, sn, codes = Q.nf3_fakequant(wd, G, want_codes=True, want_scales=True)
+        assert bits_equal(dq.cpu(), ref["dq"])
+        assert torch.equal(codes.cpu(), ref["codes"])
+        assert bits_equal(sp.cpu(), ref["scale_pos"]) and bits_equal(sn.cpu(), ref["scale_neg"])
+
+
+@pytest.mark.parametrize("dname", ["f32", "bf16"])
+def test_large_backward_vs_oracle(dname):
+    from bitdistiller_b200.quantizer import SteInt2AsymQuantizer, SteN2F3Quantizer
+    dt = DT[dname]
+    w = make_weight("randn", 256, 4096, dt, 7)
+    lim = w.float().reshape(256, -1, 128).abs().amax(-1, keepdim=True) * 0.8
+    w = torch.clamp(w.float().reshape(256, -1, 128), -lim, lim).reshape(256, 4096).to(dt)  # ties, as after apply_clip
+    gy = make_weight("uniform", 256, 4096, dt, 8)
+    for mod, orc in [(SteInt2AsymQuantizer(128), lambda: oracle.int_ste_bwd(w, gy, 128, 2)),
+                     (SteInt2AsymQuantizer(-1), lambda: oracle.int_ste_bwd(w, gy, 4096, 2)),
+                     (SteN2F3Quantizer(128), lambda: oracle.nf3_ste_bwd(w, gy, 128))]:
+        x = w.to(dev()).requires_grad_(True)
+        mod(x).backward(gy.to(dev()))
+        G = mod.q_group_size if mod.q_group_size > 0 else 4096
+        _bwd_check(x.grad, w, gy, G, orc(), dt, (dname, type(mod).__name__))
+
+
+def test_fused_clip_matches_apply_clip_then_quant():
+    from bitdistiller_b200 import quantizer as Q
+    for dname in ["bf16", "f32"]:
+        dt = DT[dname]
+        w = make_weight("randn", 128, 1024, dt, 3)
+        g = torch.Generator().manual_seed(5)
+        mx = w.float().reshape(128, -1, 128).amax(-1)
+        mn = w.float().reshape(128, -1, 128).amin(-1)
+        cmax = (mx * (1 - torch.randint(0, 10, mx.shape, generator=g) / 20)).to(dt)
+        cmin = (mn * (1 - torch.randint(0, 10, mn.shape, generator=g) / 20)).to(dt)
+        ref_i = oracle.int_fakequant(w, 128, 2, round_mode=1, clip_min=cmin, clip_max=cmax)
+        ref_n = oracle.nf3_fakequant(w, 128, clip_min=cmin, clip_max=cmax)
+        wd, a, b = w.to(dev()), cmin.to(dev()), cmax.to(dev())
+        dq, _, _, codes = Q.int_fakequant(wd, 2, 128, 1, want_codes=True, clip_min=a, clip_max=b)
+        assert bits_equal(dq.cpu(), ref_i["dq"]) and torch.equal(codes.cpu(), ref_i["codes"])
+        dqn, _, _, _ = Q.nf3_fakequant(wd, 128, clip_min=a, clip_max=b)
+        assert bits_equal(dqn.cpu(), ref_n["dq"])
+
+
+def test_cuda_eager_semantics_hypothesis(monkeypatch):
+    """BDQ_SEMANTICS=cuda must reproduce eager PyTorch ON THE GPU bit for bit, and the
+    CPU / CUDA eager results must differ exactly where the oracle's sem=0 / sem=1 differ."""
+    from bitdistiller_b200 import quantizer as Q
+    monkeypatch.setenv("BDQ_SEMANTICS", "cuda")
+    for dname in ["f32", "bf16", "f16"]:
+        dt = DT[dname]
+        w = make_weight("randn", 256, 2048, dt, 99)
+        wd = w.to(dev())
+        for bits, G, rm in [(2, 128, 0), (2, 64, 1), (4, 128, 0)]:
+            e_dq, e_s, e_z = torch_int_fakequant(wd, bits, G, bool(rm))
+            dq, s, z, _ = Q.int_fakequant(wd, bits, G, rm, want_scale_zp=True)
+            assert bits_equal(s.cpu().reshape(e_s.shape), e_s.cpu()), (dname, bits, G, rm, "scales")
+            assert bits_equal(z.cpu().reshape(e_z.shape), e_z.cpu()), (dname, bits, G, rm, "zeros")
+            assert bits_equal(dq.cpu(), e_dq.cpu()), (dname, bits, G, rm, "dq")
+            ref1 = oracle.int_fakequant(w, G, bits, round_mode=rm, sem=1)
+            assert bits_equal(dq.cpu(), ref1["dq"])
+        e = torch_nf3_fakequant(wd, 128)
+        dq, _, _, _ = Q.nf3_fakequant(wd, 128)
+        assert bits_equal(dq.cpu(), e.cpu()), (dname, "nf3")
+
+
+def test_errors_and_edge_cases():
+    from bitdistiller_b200 import _lib as L
+    from bitdistiller_b200.quantizer import SteInt2AsymQuantizer, pseudo_quantize_tensor
+    with pytest.raises(AssertionError):
+        pseudo_quantize_tensor(torch.zeros(4, 100, device=dev()), n_bit=2, q_group_size=128)
+    with pytest.raises(L.BdqError):
+        pseudo_quantize_tensor(torch.zeros(4, 128), n_bit=2, q_group_size=128)  # CPU tensor: no fallback
+    with pytest.raises(TypeError):
+        pseudo_quantize_tensor(torch.zeros(4, 128, device=dev(), dtype=torch.float64), n_bit=2, q_group_size=128)
+    e = pseudo_quantize_tensor(torch.zeros(0, 128, device=dev()), n_bit=2, q_group_size=128)
+    assert e.shape == (0, 128)
+    # 4-D input as autoclip passes it (autoclip.py:28,56), ragged tail (rows not a multiple of the warp chunk)
+    w = make_weight("randn", 3, 5 * 128, torch.bfloat16, 1).reshape(3, 1, 5, 128)
+    dq = pseudo_quantize_tensor(w.to(dev()), n_bit=2, q_group_size=128)
+    assert dq.shape == w.shape and bits_equal(dq.cpu(), oracle.int_fakequant(w, 128, 2)["dq"])
+    # non-contiguous view and unaligned base pointer
+    base = make_weight("randn", 8, 260, torch.float32, 2).to(dev())
+    v = base[:, 4:]
+    dq = pseudo_quantize_tensor(v, n_bit=2, q_group_size=128)
+    assert bits_equal(dq.cpu(), oracle.int_fakequant(v.cpu().contiguous(), 128, 2)["dq"])
+    flat = make_weight("randn", 1, 128 * 9 + 1, torch.float32, 4).to(dev()).reshape(-1)[1:].reshape(9, 128)
+    dq = pseudo_quantize_tensor(flat, n_bit=2, q_group_size=128)
+    assert bits_equal(dq.cpu(), oracle.int_fakequant(flat.cpu(), 128, 2)["dq"])
+    q = SteInt2AsymQuantizer()
+    assert q.q_group_size == 64 and q.bit == 2

@@ -1,0 +1,65 @@
+"""Developer micro-benchmark: per-kernel GB/s at BASELINE shapes (CUDA events, rotating buffers > L2)."""
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from bitdistiller_b200 import _lib as L  # noqa: E402
+from bitdistiller_b200 import quantizer as Q  # noqa: E402
+
+
+def timeit(fn, nbuf, iters=20, warm=3):
+    for i in range(warm):
+        fn(i % nbuf)
+    torch.cuda.synchronize()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(iters + 1)]
+    ev[0].record()
+    for i in range(iters):
+        fn(i % nbuf)
+        ev[i + 1].record()
+    torch.cuda.synchronize()
+    ts = sorted(ev[i].elapsed_time(ev[i + 1]) for i in range(iters))
+    return ts[len(ts) // 2] * 1e-3
+
+
+def main():
+    dev = torch.device("cuda:0")
+    peak = 6547.2
+    for dname, dt, eb in [("f32", torch.float32, 4), ("bf16", torch.bfloat16, 2)]:
+        rows, cols = (4096, 4096) if dname == "f32" else (11008, 4096)
+        nbuf = 6
+        ws = [(torch.randn(rows, cols, device=dev) * 0.02).to(dt) for _ in range(nbuf)]
+        gs = [torch.randn(rows, cols, device=dev).to(dt) for _ in range(nbuf)]
+        out = torch.empty_like(ws[0])
+        n = rows * cols
+        lib = L.lib()
+        st = L.stream_ptr(dev)
+
+        def fwd(i, rm=1, G=128):
+            lib.bdq_int_fakequant_fwd(L.ptr(ws[i]), L.ptr(out), None, None, None, None, None, L.i64(n), G, 2,
+                                      L.dtype_code(ws[i]), rm, 0, st)
+
+        def bwd(i, G=128):
+            lib.bdq_int_ste_bwd(L.ptr(ws[i]), L.ptr(gs[i]), L.ptr(out), L.i64(n), G, 2, L.dtype_code(ws[i]), 0, st)
+
+        def nfwd(i):
+            lib.bdq_nf3_fakequant_fwd(L.ptr(ws[i]), L.ptr(out), None, None, None, None, None, L.i64(n), 128,
+                                      L.dtype_code(ws[i]), 0, st)
+
+        def nbwd(i):
+            lib.bdq_nf3_ste_bwd(L.ptr(ws[i]), L.ptr(gs[i]), L.ptr(out), L.i64(n), 128, L.dtype_code(ws[i]), 0, st)
+
+        def copy(i):
+            out.copy_(ws[i])
+
+        for name, fn, bpe in [("copy", copy, 2 * eb), ("int2 fwd half-even", lambda i: fwd(i, 0), 2 * eb),
+                              ("int2 fwd half-away", fwd, 2 * eb), ("int2 fwd g64", lambda i: fwd(i, 1, 64), 2 * eb),
+                              ("int2 ste bwd", bwd, 3 * eb), ("nf3 fwd", nfwd, 2 * eb), ("nf3 bwd", nbwd, 3 * eb)]:
+            t = timeit(fn, nbuf)
+            gbs = n * bpe / t / 1e9
+            print(f"{dname} [{rows}x{cols}] {name:22s} {t*1e6:9.1f} us  {gbs:8.1f} GB/s  {gbs/peak*100:5.1f}% of measured peak")
+
+
+if __name__ == "__main__":
+    main()
