@@ -18,9 +18,15 @@ int sm_count();
 // ---- rounding of an fp32 "opmath" result to the logical tensor dtype (what eager PyTorch does between ops)
 template <int DT>
 __device__ __forceinline__ float rT(float x) {
-    if constexpr (DT == kBF16) return __bfloat162float(__float2bfloat16_rn(x));
-    else if constexpr (DT == kF16) return __half2float(__float2half_rn(x));
-    else return x;
+    if constexpr (DT == kBF16) {
+        // F2FP.BF16.F32.PACK_AB (ALU pipe) + mask instead of the scalar F2F (XU pipe)
+        __nv_bfloat162 t = __floats2bfloat162_rn(0.f, x);
+        return __uint_as_float(*reinterpret_cast<uint32_t*>(&t) & 0xffff0000u);
+    } else if constexpr (DT == kF16) {
+        return __half2float(__float2half_rn(x));
+    } else {
+        return x;
+    }
 }
 
 template <int DT>
@@ -102,10 +108,17 @@ __device__ __forceinline__ void store_scalar(void* p, int64_t i, float v) {
     else reinterpret_cast<__half*>(p)[i] = __float2half_rn(v);
 }
 
+__device__ __forceinline__ float rcp_approx(float x) {
+    float y;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
 // ---- exact division a / b (IEEE RN in fp32).
-// For 16-bit dtypes a and b carry <= 11 significant bits, so the true quotient is >= 2^-11 ulp away from any
-// fp32 rounding boundary and one residual correction with a correctly rounded reciprocal y = RN(1/b) is exact:
-//   q0 = a*y ; r = fma(-b, q0, a) (exact) ; q = RN(q0 + r*y).   Falls back to __fdiv_rn outside the safe range.
+// For 16-bit dtypes a and b carry <= 11 significant bits, so the true quotient is >= 2^-12 ulp away from any
+// fp32 rounding boundary and one residual correction with y ~= 1/b (MUFU.RCP, <= 1 ulp) is exact:
+//   q0 = a*y ; r = fma(-b, q0, a) (exact) ; q = RN(q0 + r*y)  -- the value q0 + r*y is within 2^-21 ulp of a/b.
+// Falls back to __fdiv_rn when the quotient may overflow.
 template <int DT>
 __device__ __forceinline__ float div_exact(float a, float b, float y) {
     if constexpr (DT == kF32) {
@@ -114,7 +127,7 @@ __device__ __forceinline__ float div_exact(float a, float b, float y) {
         float q0 = a * y;
         float r = __fmaf_rn(-b, q0, a);
         float q = __fmaf_rn(r, y, q0);
-        if (!(fabsf(q0) < 1e30f) || (fabsf(q0) < 1e-30f && q0 != 0.f)) q = __fdiv_rn(a, b);
+        if (!(fabsf(q0) < 1e30f)) q = __fdiv_rn(a, b);  // overflow range; tiny quotients round to 0 either way
         return q;
     }
 }
@@ -159,10 +172,15 @@ __device__ __forceinline__ IntQ int_group_params(float mx, float mn, float qmax,
     p.t1 = rT<DT>(mx - mn);
     float t2 = rT<DT>(fmaxf(p.t1, 1e-5f));
     // tensor / python scalar: CPU eager divides, CUDA eager multiplies by the fp32 reciprocal
-    float sraw = sem ? t2 * __fdiv_rn(1.0f, qmax) : __fdiv_rn(t2, qmax);
+    const float inv_q = 1.0f / qmax;  // correctly rounded (IEEE division, loop invariant)
+    float sraw;
+    if (sem) sraw = t2 * inv_q;
+    else if constexpr (DT == kF32) sraw = __fdiv_rn(t2, qmax);
+    else sraw = div_exact<DT>(t2, qmax, inv_q);
     p.s = rT<DT>(sraw);
-    p.y = __frcp_rn(p.s);
-    float t3 = rT<DT>(__fdiv_rn(mn, p.s));
+    if constexpr (DT == kF32) p.y = __frcp_rn(p.s);
+    else p.y = rcp_approx(p.s);
+    float t3 = rT<DT>(div_exact<DT>(mn, p.s, p.y));
     float z = fminf(fmaxf(-rintf(t3), 0.f), qmax);
     p.z = z + 0.f;  // -0 -> +0
     return p;

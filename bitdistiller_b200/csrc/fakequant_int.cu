@@ -8,6 +8,7 @@
 // Reference semantics: quantization/quantizer.py:25-69 (pseudo_quantize_tensor), :119-182 (Ste*AsymQuantizer),
 // backward per SURVEY.md App. B.
 #include "bdq_common.cuh"
+#include "fq_packed.cuh"
 
 namespace bdq {
 
@@ -31,7 +32,43 @@ __device__ __forceinline__ float quant_code(float x, const IntQ& p, float qmax, 
     return fminf(fmaxf(q, 0.f), qmax);
 }
 
-template <int DT, int G, int RM>
+// Process one 32-byte vector of a 16-bit dtype with packed math (see fq_packed.cuh for the exactness argument).
+// raw: input values (already clamped if clipping); returns packed dequantised values; cz[] (optional) = c - z.
+template <int DT, int RM, bool WANT_CZ>
+__device__ __forceinline__ void int_vec16_fast(const U8& raw, const IntQ& p, float qmax, U8& out, float* cz) {
+    using P = P2<DT>;
+    const typename P::h2 lo2 = P::dup(-p.z), hi2 = P::dup(qmax - p.z), s2 = P::dup(p.s);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const typename P::h2 x2 = P::from_bits(raw.r[i]);
+        float q0a, q0b;
+        const float ua = div_fast(P::lo(x2), p.s, p.y, q0a);
+        const float ub = div_fast(P::hi(x2), p.s, p.y, q0b);
+        const typename P::h2 u2 = P::pack(ua, ub);                      // rT(x / s)
+        const float ra = round_T<DT, RM>(P::lo(u2)), rb = round_T<DT, RM>(P::hi(u2));
+        const typename P::h2 cz2 = __hmin2(__hmax2(P::pack(ra, rb), lo2), hi2);  // clamp(r + z, 0, qmax) - z
+        out.r[i] = P::bits(__hmul2(cz2, s2));                           // rT((c - z) * s)
+        if constexpr (WANT_CZ) { cz[2 * i] = P::lo(cz2); cz[2 * i + 1] = P::hi(cz2); }
+    }
+}
+
+// op-by-op path for one vector (groups whose quotients may overflow, or bits > 6); rarely executed
+template <int DT, int RM>
+__device__ __noinline__ void int_vec_slow(const U8& raw, const IntQ& p, float qmax, U8& out, float* czs) {
+    constexpr int VEC = VecN<DT>::v;
+    float f[VEC], o[VEC];
+    unpack<DT>(raw, f);
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) {
+        float qu;
+        float c = quant_code<DT, RM>(f[i], p, qmax, qu);
+        czs[i] = c - p.z;
+        o[i] = czs[i] * p.s;
+    }
+    pack<DT>(o, out);
+}
+
+template <int DT, int G, int RM, bool FAST, bool AUX, bool CLIP>
 __global__ void __launch_bounds__(kThreads) int_fq_fwd_kernel(
     const uint8_t* __restrict__ w, uint8_t* __restrict__ dq, void* __restrict__ scales, void* __restrict__ zeros,
     uint8_t* __restrict__ codes, const void* __restrict__ cmin, const void* __restrict__ cmax, int64_t nvec,
@@ -61,49 +98,79 @@ __global__ void __launch_bounds__(kThreads) int_fq_fwd_kernel(
         for (int u = 0; u < kUnroll; ++u) {
             const int64_t v = (c0 + u) * 32 + lane;
             const int64_t g = v / LPG;
-            float f[VEC];
-            unpack<DT>(raw[u], f);
-            if (cmin != nullptr && valid[u]) {
-                float lo = load_scalar<DT>(cmin, g), hi = load_scalar<DT>(cmax, g);
+            float mx, mn;
+            U8 out;
+            float czs[VEC];
+            IntQ p;
+            if constexpr (DT != kF32) {
+                using P = P2<DT>;
+                if constexpr (CLIP) {
+                    if (valid[u]) {
+                        const typename P::h2 l2 = P::dup(load_scalar<DT>(cmin, g)), h2v = P::dup(load_scalar<DT>(cmax, g));
 #pragma unroll
-                for (int i = 0; i < VEC; ++i) f[i] = fminf(fmaxf(f[i], lo), hi);
-            }
-            float mx = f[0], mn = f[0];
+                        for (int i = 0; i < 8; ++i) raw[u].r[i] = P::bits(__hmin2(__hmax2(P::from_bits(raw[u].r[i]), l2), h2v));
+                    }
+                }
+                vec_minmax16<DT>(raw[u], mx, mn);
+                mx = group_max<LPG>(mx);
+                mn = group_min<LPG>(mn);
+                p = int_group_params<DT>(mx, mn, qmax, sem);
+                const bool safe = FAST && (fmaxf(fabsf(mx), fabsf(mn)) * p.y < 1e30f);
+                if (safe) {
+                    int_vec16_fast<DT, RM, AUX>(raw[u], p, qmax, out, czs);
+                } else {
+                    int_vec_slow<DT, RM>(raw[u], p, qmax, out, czs);
+                }
+            } else {
+                float f[VEC], o[VEC];
+                unpack<DT>(raw[u], f);
+                if constexpr (CLIP) {
+                    if (valid[u]) {
+                        float lo = load_scalar<DT>(cmin, g), hi = load_scalar<DT>(cmax, g);
 #pragma unroll
-            for (int i = 1; i < VEC; ++i) { mx = fmaxf(mx, f[i]); mn = fminf(mn, f[i]); }
-            mx = group_max<LPG>(mx);
-            mn = group_min<LPG>(mn);
-            const IntQ p = int_group_params<DT>(mx, mn, qmax, sem);
-            float o[VEC];
-            uint32_t cw[VEC / 4];
+                        for (int i = 0; i < VEC; ++i) f[i] = fminf(fmaxf(f[i], lo), hi);
+                    }
+                }
+                mx = f[0];
+                mn = f[0];
 #pragma unroll
-            for (int i = 0; i < VEC / 4; ++i) cw[i] = 0;
+                for (int i = 1; i < VEC; ++i) { mx = fmaxf(mx, f[i]); mn = fminf(mn, f[i]); }
+                mx = group_max<LPG>(mx);
+                mn = group_min<LPG>(mn);
+                p = int_group_params<DT>(mx, mn, qmax, sem);
 #pragma unroll
-            for (int i = 0; i < VEC; ++i) {
-                float qu;
-                float c = quant_code<DT, RM>(f[i], p, qmax, qu);
-                o[i] = (c - p.z) * p.s;  // rounded to T by pack()
-                cw[i / 4] |= ((uint32_t)c & 0xffu) << (8 * (i % 4));
+                for (int i = 0; i < VEC; ++i) {
+                    float qu;
+                    float c = quant_code<DT, RM>(f[i], p, qmax, qu);
+                    czs[i] = c - p.z;
+                    o[i] = czs[i] * p.s;
+                }
+                pack<DT>(o, out);
             }
             if (valid[u]) {
-                U8 out;
-                pack<DT>(o, out);
                 stg256(dq + v * 32, out);
-                if (codes != nullptr) {
-                    uint32_t* cp = reinterpret_cast<uint32_t*>(codes + v * VEC);
+                if constexpr (AUX) {
+                    if (codes != nullptr) {
+                        uint32_t* cp = reinterpret_cast<uint32_t*>(codes + v * VEC);
 #pragma unroll
-                    for (int i = 0; i < VEC / 4; ++i) cp[i] = cw[i];
-                }
-                if ((lane % LPG) == 0) {
-                    if (scales != nullptr) store_scalar<DT>(scales, g, p.s);
-                    if (zeros != nullptr) store_scalar<DT>(zeros, g, p.z);
+                        for (int i = 0; i < VEC / 4; ++i) {
+                            uint32_t cw = 0;
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) cw |= ((uint32_t)(czs[4 * i + j] + p.z) & 0xffu) << (8 * j);
+                            cp[i] = cw;
+                        }
+                    }
+                    if ((lane % LPG) == 0) {
+                        if (scales != nullptr) store_scalar<DT>(scales, g, p.s);
+                        if (zeros != nullptr) store_scalar<DT>(zeros, g, p.z);
+                    }
                 }
             }
         }
     }
 }
 
-template <int DT, int G>
+template <int DT, int G, bool FAST>
 __global__ void __launch_bounds__(kThreads) int_ste_bwd_kernel(
     const uint8_t* __restrict__ w, const uint8_t* __restrict__ gy, uint8_t* __restrict__ gw, int64_t nvec,
     float qmax, int sem) {
@@ -136,24 +203,54 @@ __global__ void __launch_bounds__(kThreads) int_ste_bwd_kernel(
             float f[VEC], g[VEC];
             unpack<DT>(rw[u], f);
             unpack<DT>(rg[u], g);
-            float mx = f[0], mn = f[0];
+            float mx, mn;
+            if constexpr (DT != kF32) {
+                vec_minmax16<DT>(rw[u], mx, mn);
+            } else {
+                mx = f[0];
+                mn = f[0];
 #pragma unroll
-            for (int i = 1; i < VEC; ++i) { mx = fmaxf(mx, f[i]); mn = fminf(mn, f[i]); }
+                for (int i = 1; i < VEC; ++i) { mx = fmaxf(mx, f[i]); mn = fminf(mn, f[i]); }
+            }
             mx = group_max<LPG>(mx);
             mn = group_min<LPG>(mn);
             const IntQ p = int_group_params<DT>(mx, mn, qmax, sem);
+            const float lo = -p.z, hi = qmax - p.z;
             float Gs = 0.f;
             int cnt = 0;  // low 16 bits: #(x == max), high 16 bits: #(x == min)
             uint32_t mbits = 0;
+            bool safe = false;
+            if constexpr (DT != kF32) safe = FAST && (fmaxf(fabsf(mx), fabsf(mn)) * p.y < 1e30f);
+            if (safe) {
+                if constexpr (DT != kF32) {
+                    using P = P2<DT>;
 #pragma unroll
-            for (int i = 0; i < VEC; ++i) {
-                float qu;
-                float c = quant_code<DT, BDQ_ROUND_HALF_AWAY>(f[i], p, qmax, qu);
-                bool m = (qu >= 0.f) && (qu <= qmax);  // clamp backward: closed interval
-                mbits |= (m ? 1u : 0u) << i;
-                Gs += g[i] * ((c - p.z) - (m ? f[i] * p.y : 0.f));
-                cnt += (f[i] == mx ? 1 : 0) + (f[i] == mn ? 65536 : 0);
+                    for (int i = 0; i < VEC; i += 2) {
+                        float q0a, q0b;
+                        const float ua = div_fast(f[i], p.s, p.y, q0a);
+                        const float ub = div_fast(f[i + 1], p.s, p.y, q0b);
+                        const typename P::h2 u2 = P::pack(ua, ub);
+                        const float ra = round_T<DT, BDQ_ROUND_HALF_AWAY>(P::lo(u2));
+                        const float rb = round_T<DT, BDQ_ROUND_HALF_AWAY>(P::hi(u2));
+                        const bool ma = (ra >= lo) && (ra <= hi), mb = (rb >= lo) && (rb <= hi);
+                        mbits |= (ma ? 1u : 0u) << i;
+                        mbits |= (mb ? 1u : 0u) << (i + 1);
+                        Gs += g[i] * (fminf(fmaxf(ra, lo), hi) - (ma ? q0a : 0.f));
+                        Gs += g[i + 1] * (fminf(fmaxf(rb, lo), hi) - (mb ? q0b : 0.f));
+                    }
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < VEC; ++i) {
+                    float qu;
+                    float c = quant_code<DT, BDQ_ROUND_HALF_AWAY>(f[i], p, qmax, qu);
+                    bool m = (qu >= 0.f) && (qu <= qmax);  // clamp backward: closed interval
+                    mbits |= (m ? 1u : 0u) << i;
+                    Gs += g[i] * ((c - p.z) - (m ? f[i] * p.y : 0.f));
+                }
             }
+#pragma unroll
+            for (int i = 0; i < VEC; ++i) cnt += (f[i] == mx ? 1 : 0) + (f[i] == mn ? 65536 : 0);
             Gs = group_sum<LPG>(Gs);
             cnt = group_sum_i<LPG>(cnt);
             const float gs = (p.t1 >= 1e-5f) ? Gs * inv_qmax : 0.f;  // clamp(min=1e-5) cuts the scale path
@@ -249,6 +346,14 @@ static int grid_for(int64_t work_warps, int unroll) {
     return (int)blocks;
 }
 
+template <int DT, int RM, bool FAST, bool AUX, bool CLIP>
+static void launch_fwd_g(const uint8_t* wp, uint8_t* op, void* scales, void* zeros, uint8_t* codes, const void* cmin,
+                         const void* cmax, int64_t nvec, int G, float qmax, int sem, int grid, cudaStream_t st) {
+    if (G == 128) int_fq_fwd_kernel<DT, 128, RM, FAST, AUX, CLIP><<<grid, kThreads, 0, st>>>(wp, op, scales, zeros, codes, cmin, cmax, nvec, qmax, sem);
+    else if (G == 64) int_fq_fwd_kernel<DT, 64, RM, FAST, AUX, CLIP><<<grid, kThreads, 0, st>>>(wp, op, scales, zeros, codes, cmin, cmax, nvec, qmax, sem);
+    else int_fq_fwd_kernel<DT, 32, RM, FAST, AUX, CLIP><<<grid, kThreads, 0, st>>>(wp, op, scales, zeros, codes, cmin, cmax, nvec, qmax, sem);
+}
+
 template <int DT, int RM>
 static int launch_fwd(const void* w, void* dq, void* scales, void* zeros, uint8_t* codes, const void* cmin,
                       const void* cmax, int64_t n, int G, float qmax, int sem, cudaStream_t st) {
@@ -260,14 +365,32 @@ static int launch_fwd(const void* w, void* dq, void* scales, void* zeros, uint8_
         int grid = grid_for((nvec + 31) / 32, kUnroll);
         const uint8_t* wp = (const uint8_t*)w;
         uint8_t* op = (uint8_t*)dq;
-        if (G == 128) int_fq_fwd_kernel<DT, 128, RM><<<grid, kThreads, 0, st>>>(wp, op, scales, zeros, codes, cmin, cmax, nvec, qmax, sem);
-        else if (G == 64) int_fq_fwd_kernel<DT, 64, RM><<<grid, kThreads, 0, st>>>(wp, op, scales, zeros, codes, cmin, cmax, nvec, qmax, sem);
-        else int_fq_fwd_kernel<DT, 32, RM><<<grid, kThreads, 0, st>>>(wp, op, scales, zeros, codes, cmin, cmax, nvec, qmax, sem);
+        const bool aux = scales || zeros || codes;
+        const bool clip = cmin != nullptr;
+        const bool fast = qmax <= 63.f;  // packed rounding identity holds for bits <= 6 (fq_packed.cuh)
+        if (!aux && !clip) {
+            if (fast) launch_fwd_g<DT, RM, true, false, false>(wp, op, scales, zeros, codes, cmin, cmax, nvec, G, qmax, sem, grid, st);
+            else launch_fwd_g<DT, RM, false, false, false>(wp, op, scales, zeros, codes, cmin, cmax, nvec, G, qmax, sem, grid, st);
+        } else if (!clip) {
+            if (fast) launch_fwd_g<DT, RM, true, true, false>(wp, op, scales, zeros, codes, cmin, cmax, nvec, G, qmax, sem, grid, st);
+            else launch_fwd_g<DT, RM, false, true, false>(wp, op, scales, zeros, codes, cmin, cmax, nvec, G, qmax, sem, grid, st);
+        } else {
+            if (fast) launch_fwd_g<DT, RM, true, true, true>(wp, op, scales, zeros, codes, cmin, cmax, nvec, G, qmax, sem, grid, st);
+            else launch_fwd_g<DT, RM, false, true, true>(wp, op, scales, zeros, codes, cmin, cmax, nvec, G, qmax, sem, grid, st);
+        }
     } else {
         int grid = grid_for(n / G, 1);
         int_generic_kernel<DT, RM, false><<<grid, kThreads, 0, st>>>(w, nullptr, dq, scales, zeros, codes, cmin, cmax, n / G, G, qmax, sem);
     }
     return check_launch("bdq_int_fakequant_fwd");
+}
+
+template <int DT, bool FAST>
+static void launch_bwd_g(const uint8_t* wp, const uint8_t* gp, uint8_t* op, int64_t nvec, int G, float qmax, int sem,
+                         int grid, cudaStream_t st) {
+    if (G == 128) int_ste_bwd_kernel<DT, 128, FAST><<<grid, kThreads, 0, st>>>(wp, gp, op, nvec, qmax, sem);
+    else if (G == 64) int_ste_bwd_kernel<DT, 64, FAST><<<grid, kThreads, 0, st>>>(wp, gp, op, nvec, qmax, sem);
+    else int_ste_bwd_kernel<DT, 32, FAST><<<grid, kThreads, 0, st>>>(wp, gp, op, nvec, qmax, sem);
 }
 
 template <int DT>
@@ -279,9 +402,8 @@ static int launch_bwd(const void* w, const void* gy, void* gw, int64_t n, int G,
         int grid = grid_for((nvec + 31) / 32, kUnroll);
         const uint8_t *wp = (const uint8_t*)w, *gp = (const uint8_t*)gy;
         uint8_t* op = (uint8_t*)gw;
-        if (G == 128) int_ste_bwd_kernel<DT, 128><<<grid, kThreads, 0, st>>>(wp, gp, op, nvec, qmax, sem);
-        else if (G == 64) int_ste_bwd_kernel<DT, 64><<<grid, kThreads, 0, st>>>(wp, gp, op, nvec, qmax, sem);
-        else int_ste_bwd_kernel<DT, 32><<<grid, kThreads, 0, st>>>(wp, gp, op, nvec, qmax, sem);
+        if (qmax <= 63.f) launch_bwd_g<DT, true>(wp, gp, op, nvec, G, qmax, sem, grid, st);
+        else launch_bwd_g<DT, false>(wp, gp, op, nvec, G, qmax, sem, grid, st);
     } else {
         int grid = grid_for(n / G, 1);
         int_generic_kernel<DT, BDQ_ROUND_HALF_AWAY, true><<<grid, kThreads, 0, st>>>(w, gy, gw, nullptr, nullptr, nullptr, nullptr, nullptr, n / G, G, qmax, sem);
