@@ -89,6 +89,38 @@ int bdq_nf3_ste_bwd(const void* w, const void* gy, void* gw, int64_t n_elem, int
 int bdq_apply_clip(void* w, const void* clip_min, const void* clip_max, int64_t n_elem, int group, int dtype,
                    bdq_stream_t stream);
 
+/*
+ * calculate_zeros_width (quantization/qmodule.py:16-28): int32 words per row of qzeros; -1 for an unsupported group.
+ * Host-only helper, no CUDA call.
+ */
+int bdq_zeros_width(int64_t in_features, int group, int w_bit);
+
+/*
+ * Real quantise + pack = WQLinear.from_linear (quantization/qmodule.py:70-146), one pass instead of
+ * in_features + 2*in_features/pack tiny eager kernels.
+ * w_dq [rows*cols] (T): the fake-quantised weight (output of pseudo_quantize_tensor, quantizer.py:96);
+ * scales, zeros [rows*cols/group] (T).  Outputs (caller-allocated): qweight int32 [rows, cols*w_bit/32],
+ * qzeros int32 [rows, zw], qscales fp16 [rows, zw*32/w_bit] (zero-padded), zw = bdq_zeros_width().
+ * Codes are packed sequentially: bits [i*w_bit, (i+1)*w_bit) of qweight[r, c] = code of column c*pack+i.
+ * w_bit in {2, 4}.
+ */
+int bdq_pack_wq(const void* w_dq, const void* scales, const void* zeros, int32_t* qweight, int32_t* qzeros,
+                void* qscales, int64_t rows, int64_t cols, int group, int w_bit, int dtype, bdq_stream_t stream);
+
+/*
+ * Packed 2-bit decode GEMV: out[b, oc] = fp16( sum_k x[b,k] * scales[oc,k/G] * (code[oc,k] - zero[oc,k/G]) ),
+ * fp32 accumulation.  Replaces gemv_forward_cuda / gemv_kernel_g128_2bit
+ * (inference/kernels/csrc/quantization/gemv_cuda.cu:202-272, 289-346; pybind.cpp:13).
+ * x [B, IC] fp16, qweight/qzeros/scales as produced by bdq_pack_wq (w_bit 2), out [B, OC] fp16.
+ * group in {64, 128}, IC % 128 == 0, OC % 16 == 0, any B >= 1 (weights are streamed once per 8 rows of x).
+ * Bounds are checked against IC (the reference kernel reads past the row end when IC % 2048 != 0).
+ * flags: BDQ_GEMV_PDL = launch with programmatic stream serialisation (the weight prefetch of this launch
+ * overlaps the tail of the previous kernel on the stream; x is read only after the dependency resolves).
+ */
+#define BDQ_GEMV_PDL 1
+int bdq_gemv_w2(const void* x, const int32_t* qweight, const void* scales, const int32_t* qzeros, void* out,
+                int64_t B, int64_t IC, int64_t OC, int group, int flags, bdq_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

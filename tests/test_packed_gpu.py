@@ -1,0 +1,135 @@
+"""GPU parity tests for the deploy side of the path: real-quantise + pack (WQLinear.from_linear) and the packed int2
+GEMV, through the C ABI via the reference-named Python modules.  Packed bytes / zeros / scales: bit-exact.
+GEMV outputs: rtol 1e-2 (BASELINE.json north_star), checked against the double-precision oracle."""
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from _util import DT, load_cases, make_weight, t
+
+pytestmark = pytest.mark.gpu
+dev = torch.device("cuda:0")
+
+
+def test_pack_golden_bit_exact():
+    from bitdistiller_b200.qmodule import WQLinear
+    n = 0
+    for meta, c in load_cases("pack"):
+        dname, w_bit, G = meta[0], int(meta[1]), int(meta[2])
+        dt = DT[dname]
+        dq, s, z = t(c["dq"], dt).to(dev), t(c["s"], dt).to(dev), t(c["z"], dt).to(dev)
+        rows, cols = dq.shape
+        lin = torch.nn.Linear(cols, rows, bias=(n % 2 == 0), dtype=dt, device=dev)
+        lin.weight.data = dq
+        ql = WQLinear.from_linear(lin, w_bit, G, False, s, z)
+        assert ql.qweight.dtype == torch.int32 and ql.qzeros.dtype == torch.int32 and ql.scales.dtype == torch.float16
+        assert np.array_equal(ql.qweight.cpu().numpy(), c["qweight"]), meta
+        assert np.array_equal(ql.qzeros.cpu().numpy(), c["qzeros"]), meta
+        assert np.array_equal(ql.scales.float().cpu().numpy(), c["qscales"]), meta
+        if lin.bias is not None:
+            assert ql.bias.dtype == torch.float16 and torch.equal(ql.bias, lin.bias.half())
+        n += 1
+    assert n == 18
+
+
+@pytest.mark.parametrize("dname", ["f16", "bf16", "f32"])
+def test_pack_large_vs_oracle_and_roundtrip(dname):
+    """[256, 11008] (ragged: 86 groups -> zeros width 6, scales padded to 96): bytes equal the oracle's, unpacked codes
+    equal the fake-quant codes (format spec)."""
+    from bitdistiller_b200 import quantizer as Q
+    from bitdistiller_b200.qmodule import pack_wq
+    dt = DT[dname]
+    w = make_weight("randn", 256, 11008, dt, 11)
+    wd = w.to(dev)
+    dq, s, z, codes = Q.int_fakequant(wd, 2, 128, 0, want_scale_zp=True, want_codes=True)
+    qw, qz, qs = pack_wq(dq, s.view(256, -1), z.view(256, -1), 2, 128)
+    rw, rz, rs = oracle.pack(dq.cpu(), s.view(256, -1).cpu(), z.view(256, -1).cpu(), 128, 2)
+    assert torch.equal(qw.cpu(), rw) and torch.equal(qz.cpu(), rz) and torch.equal(qs.cpu(), rs)
+    assert qz.shape == (256, 6) and qs.shape == (256, 96)
+    un = (qw.cpu().numpy().view(np.uint32)[:, :, None] >> (np.arange(16, dtype=np.uint32) * 2)) & 3
+    assert np.array_equal(un.reshape(256, 11008), codes.cpu().numpy())
+
+
+def _packed_layer(oc, ic, seed, G=128):
+    from bitdistiller_b200 import quantizer as Q
+    from bitdistiller_b200.qmodule import pack_wq
+    w = make_weight("randn", oc, ic, torch.float16, seed).to(dev)
+    dq, s, z, _ = Q.int_fakequant(w, 2, G, 0, want_scale_zp=True)
+    return pack_wq(dq, s.view(oc, -1), z.view(oc, -1), 2, G), dq
+
+
+def _check_gemv(out, ref, x, dq):
+    """rtol 1e-2 against the oracle, with an absolute floor tied to the fp16 output rounding and the size of the
+    terms of the dot product (outputs near zero come from cancellation)."""
+    out, ref = out.double().cpu(), ref.double().cpu()
+    scale = (x.double().cpu().abs() @ dq.double().cpu().abs().T)  # sum_k |x_k w_k|
+    tol = 1e-2 * ref.abs() + 2e-3 * scale / np.sqrt(x.shape[1]) + 1e-6
+    bad = (out - ref).abs() > tol
+    assert not bool(bad.any()), (int(bad.sum()), float((out - ref).abs().max()))
+    # and tight in aggregate: relative Frobenius error far below the bar
+    assert float((out - ref).norm() / ref.norm()) < 2e-3
+
+
+@pytest.mark.parametrize("oc,ic", [(4096, 4096), (1024, 4096), (12288, 4096), (4096, 12288), (4096, 11008), (64, 128)])
+@pytest.mark.parametrize("pdl", [False, True])
+def test_gemv_w2_vs_oracle(oc, ic, pdl):
+    from bitdistiller_b200 import awq_inference_engine as E
+    (qw, qz, qs), dq = _packed_layer(oc, ic, 21)
+    g = torch.Generator().manual_seed(5)
+    x = torch.randn(1, ic, generator=g).to(torch.float16).to(dev)
+    out = E.gemv_forward_cuda(x, qw, qs, qz, 2, 128, pdl=pdl)
+    assert out.shape == (1, oc) and out.dtype == torch.float16
+    sub = slice(0, min(oc, 512))   # the CPU oracle is O(OC*IC): check a slab of channels plus the tail
+    ref = oracle.wq_matmul(x.cpu(), qw[sub].cpu(), qz[sub].cpu(), qs[sub].cpu(), 128, 2)
+    _check_gemv(out[:, sub], ref, x, dq[sub])
+    ref_t = oracle.wq_matmul(x.cpu(), qw[-64:].cpu(), qz[-64:].cpu(), qs[-64:].cpu(), 128, 2)
+    _check_gemv(out[:, -64:], ref_t, x, dq[-64:])
+    # whole output against dequantised fp32 matmul on the GPU (same math, different summation order)
+    full = (x.float() @ dq.float().T)
+    assert float((out.float() - full).norm() / full.norm()) < 2e-3
+
+
+@pytest.mark.parametrize("B", [2, 5, 8, 11])
+def test_gemv_w2_batched(B):
+    from bitdistiller_b200 import awq_inference_engine as E
+    (qw, qz, qs), dq = _packed_layer(512, 4096, 33)
+    x = torch.randn(B, 4096, generator=torch.Generator().manual_seed(B)).to(torch.float16).to(dev)
+    out = E.gemv_forward_cuda(x, qw, qs, qz, 2, 128)
+    ref = oracle.wq_matmul(x.cpu(), qw.cpu(), qz.cpu(), qs.cpu(), 128, 2)
+    _check_gemv(out, ref, x, dq)
+
+
+def test_gemv_w2_group64_generic_and_errors():
+    from bitdistiller_b200 import _lib as L
+    from bitdistiller_b200 import awq_inference_engine as E
+    (qw, qz, qs), dq = _packed_layer(128, 1024, 44, G=64)
+    x = torch.randn(2, 1024, generator=torch.Generator().manual_seed(1)).to(torch.float16).to(dev)
+    out = E.gemv_forward_cuda(x, qw, qs, qz, 2, 64)
+    ref = oracle.wq_matmul(x.cpu(), qw.cpu(), qz.cpu(), qs.cpu(), 64, 2)
+    _check_gemv(out, ref, x, dq)
+    with pytest.raises(NotImplementedError):
+        E.gemv_forward_cuda(x, qw, qs, qz, 4, 64)
+    with pytest.raises(TypeError):
+        E.gemv_forward_cuda(x.float(), qw, qs, qz, 2, 64)
+    with pytest.raises(L.BdqError):
+        E.gemv_forward_cuda(x.cpu(), qw, qs, qz, 2, 64)
+
+
+def test_wqlinear_forward_decode_matches_dequant():
+    """WQLinear end to end: real_quantize_model_weight-style construction, forward with 1 row and with bias."""
+    from bitdistiller_b200.quantizer import pseudo_quantize_tensor
+    from bitdistiller_b200.qmodule import WQLinear
+    lin = torch.nn.Linear(4096, 1024, bias=True, dtype=torch.float16, device=dev)
+    lin.weight.data = make_weight("randn", 1024, 4096, torch.float16, 3).to(dev)
+    lin.weight.data, s, z = pseudo_quantize_tensor(lin.weight.data, n_bit=2, q_group_size=128, get_scale_zp=True)
+    ql = WQLinear.from_linear(lin, 2, 128, False, s, z)
+    x = torch.randn(1, 1, 4096, device=dev, dtype=torch.float16)
+    y = ql(x)
+    ref = torch.nn.functional.linear(x.float(), lin.weight.data.float(), lin.bias.float())
+    assert y.shape == (1, 1, 1024)
+    assert float((y.float() - ref).norm() / ref.norm()) < 3e-3
+    sd = ql.state_dict()
+    assert set(sd) == {"qweight", "qzeros", "scales", "bias"}
+    with pytest.raises(NotImplementedError):
+        WQLinear(3, 128, 128, 128, False, dev)
