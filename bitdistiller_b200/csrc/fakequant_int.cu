@@ -9,28 +9,18 @@
 // backward per SURVEY.md App. B.
 #include "bdq_common.cuh"
 #include "fq_packed.cuh"
+#include "fq_int_elem.cuh"
 
 namespace bdq {
 
+// threshold-formulated kernels for 16-bit dtypes, bits 2/3 (fakequant_thr.cu); return false if not applicable
+bool launch_int_thr_fwd(const void* w, void* dq, const void* cmin, const void* cmax, int64_t n, int G, int bits, int dtype,
+                        int round_mode, int sem, cudaStream_t st);
+bool launch_int_thr_bwd(const void* w, const void* gy, void* gw, int64_t n, int G, int bits, int dtype, int sem,
+                        cudaStream_t st);
+
 constexpr int kThreads = 256;
 constexpr int kUnroll = 2;  // 32-byte vectors in flight per lane
-
-template <int DT, int RM>
-__device__ __forceinline__ float quant_code(float x, const IntQ& p, float qmax, float& q_unclamped) {
-    float u = rT<DT>(div_exact<DT>(x, p.s, p.y));
-    float r;
-    if constexpr (RM == BDQ_ROUND_HALF_AWAY) {
-        // Round.forward (quantizer.py:14-17): sign(u) * floor(rT(|u| + 0.5)); the product and the later
-        // r + z, c - z are exact in T for every bit width <= 8 (integers below 2^8), see DESIGN.md.
-        float a = rT<DT>(fabsf(u) + 0.5f);
-        r = copysignf(floorf(a), u);
-    } else {
-        r = rintf(u);  // torch.round: half to even
-    }
-    float q = r + p.z;
-    q_unclamped = q;
-    return fminf(fmaxf(q, 0.f), qmax);
-}
 
 // Process one 32-byte vector of a 16-bit dtype with packed math (see fq_packed.cuh for the exactness argument).
 // raw: input values (already clamped if clipping); returns packed dequantised values; cz[] (optional) = c - z.
@@ -50,22 +40,6 @@ __device__ __forceinline__ void int_vec16_fast(const U8& raw, const IntQ& p, flo
         out.r[i] = P::bits(__hmul2(cz2, s2));                           // rT((c - z) * s)
         if constexpr (WANT_CZ) { cz[2 * i] = P::lo(cz2); cz[2 * i + 1] = P::hi(cz2); }
     }
-}
-
-// op-by-op path for one vector (groups whose quotients may overflow, or bits > 6); rarely executed
-template <int DT, int RM>
-__device__ __noinline__ void int_vec_slow(const U8& raw, const IntQ& p, float qmax, U8& out, float* czs) {
-    constexpr int VEC = VecN<DT>::v;
-    float f[VEC], o[VEC];
-    unpack<DT>(raw, f);
-#pragma unroll
-    for (int i = 0; i < VEC; ++i) {
-        float qu;
-        float c = quant_code<DT, RM>(f[i], p, qmax, qu);
-        czs[i] = c - p.z;
-        o[i] = czs[i] * p.s;
-    }
-    pack<DT>(o, out);
 }
 
 template <int DT, int G, int RM, bool FAST, bool AUX, bool CLIP>
@@ -432,6 +406,9 @@ extern "C" int bdq_int_fakequant_fwd(const void* w, void* dq, void* scales, void
     if (!w || !dq) { set_error("null tensor pointer"); return BDQ_ERR_SHAPE; }
     const float qmax = (float)((1 << bits) - 1);
     cudaStream_t st = (cudaStream_t)stream;
+    if (!scales && !zeros && !codes &&
+        launch_int_thr_fwd(w, dq, clip_min, clip_max, n_elem, group, bits, dtype, round_mode, sem, st))
+        return check_launch("bdq_int_fakequant_fwd(thr)");
 #define BDQ_FWD(DT)                                                                                                   \
     return round_mode == BDQ_ROUND_HALF_AWAY                                                                           \
                ? launch_fwd<DT, BDQ_ROUND_HALF_AWAY>(w, dq, scales, zeros, codes, clip_min, clip_max, n_elem, group, qmax, sem, st) \
@@ -450,6 +427,7 @@ extern "C" int bdq_int_ste_bwd(const void* w, const void* gy, void* gw, int64_t 
     if (!w || !gy || !gw) { set_error("null tensor pointer"); return BDQ_ERR_SHAPE; }
     const float qmax = (float)((1 << bits) - 1);
     cudaStream_t st = (cudaStream_t)stream;
+    if (launch_int_thr_bwd(w, gy, gw, n_elem, group, bits, dtype, sem, st)) return check_launch("bdq_int_ste_bwd(thr)");
     if (dtype == BDQ_F32) return launch_bwd<kF32>(w, gy, gw, n_elem, group, qmax, sem, st);
     if (dtype == BDQ_BF16) return launch_bwd<kBF16>(w, gy, gw, n_elem, group, qmax, sem, st);
     return launch_bwd<kF16>(w, gy, gw, n_elem, group, qmax, sem, st);

@@ -47,7 +47,12 @@ def test_pseudo_quantize_tensor_golden_bit_exact():
 def _bwd_check(gw, w, gy, G, ref64, dt, meta):
     """|ours - closed form(double)| bounded by the rounding of the output dtype plus fp32 accumulation noise."""
     gw = gw.double().cpu()
-    tol = 1.01 * ulp_of(ref64, dt) + 1e-30
+    # elements equal to their group's max / min also receive the amax / amin (scale-path) gradient: the packed kernels
+    # add it as a hi + lo pair of T values (two roundings, <= 1 ulp each way); the reference's own T-dtype autograd
+    # accumulates these terms with three roundings.
+    wg = w.double().reshape(-1, G)
+    ext = ((wg == wg.amax(1, keepdim=True)) | (wg == wg.amin(1, keepdim=True))).reshape(ref64.shape)
+    tol = torch.where(ext, 2.01, 1.01) * ulp_of(ref64, dt) + 1e-30
     gsum = gy.double().abs().reshape(-1, G).sum(1, keepdim=True).expand(-1, G).reshape(ref64.shape)
     tol = tol + 1e-5 * gsum
     bad = (gw - ref64).abs() > tol
