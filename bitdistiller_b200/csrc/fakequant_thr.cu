@@ -157,7 +157,7 @@ __device__ __noinline__ void int_bwd_slow_phase2(const void* w, const void* gy, 
 }
 
 template <int DT, int G, int NT>
-__global__ void __launch_bounds__(kThrThreads) int_thr_bwd_kernel(const uint8_t* __restrict__ w, const uint8_t* __restrict__ gy,
+__global__ void __launch_bounds__(kThrThreads, 4) int_thr_bwd_kernel(const uint8_t* __restrict__ w, const uint8_t* __restrict__ gy,
                                                                   uint8_t* __restrict__ gw, int64_t nchunk, int sem) {
     using P = P2<DT>;
     using h2 = typename P::h2;

@@ -121,6 +121,24 @@ int bdq_pack_wq(const void* w_dq, const void* scales, const void* zeros, int32_t
 int bdq_gemv_w2(const void* x, const int32_t* qweight, const void* scales, const int32_t* qzeros, void* out,
                 int64_t B, int64_t IC, int64_t OC, int group, int flags, bdq_stream_t stream);
 
+/*
+ * Two-sided clip-ratio grid search = auto_2clip_layer (quantization/autoclip.py:13-83), all candidates of all
+ * (output channel, group) pairs in one launch.  w [co, ci] (T, row-major); x = the calibration activations
+ * [n_tok, ci] of the same dtype with a row stride of x_row_stride elements (the reference's token sub-sampling
+ * x[:, 0::n_tok//512], autoclip.py:27, is a stride here, not a copy).  For every (o, g) and every candidate
+ * (i_p, i_n), i_* in [0, int(max_shrink*n_grid)):  max' = max*(1 - i_p/n_grid), min' = min*(1 - i_n/n_grid),
+ * err = mean_t (sum_k x[t,g,k] * (Q(clamp(w[o,g,:], min', max'))[k] - w[o,g,k]))^2 with Q = pseudo_quantize_tensor
+ * (quant_type BDQ_QUANT_INT, `bits`) or pseudo_quantize_n2f3_tensor (BDQ_QUANT_NF3); the first candidate with the
+ * smallest error in (i_p outer, i_n inner) order wins (strict '<' update from 1e9, autoclip.py:45,69-72).
+ * Candidate weights carry the exact T roundings of the reference; the contraction over k runs on the tensor cores
+ * with fp32 accumulation (the reference contracts in T).  Outputs: best_max, best_min [co * ci/group] (T) = the
+ * reference's return values flattened; optional best_idx (i_p*nc + i_n, or -1 if no candidate improved on 1e9 / all NaN)
+ * and best_err (fp32 mean squared error of the winner).  group in {32, 64, 128}; nc*nc <= 111.
+ */
+int bdq_autoclip(const void* w, const void* x, void* best_max, void* best_min, int32_t* best_idx, float* best_err,
+                 int64_t co, int64_t ci, int64_t n_tok, int64_t x_row_stride, int group, int bits, int quant_type,
+                 int n_grid, double max_shrink, int dtype, int sem, bdq_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,101 @@
+"""GPU parity tests for the clip-ratio search (auto_2clip_layer, autoclip.py:13-83) through the C ABI.
+
+Parity metric (the reference's own bf16 contraction is noise-limited, exact index agreement with it is
+not defined): against the double-precision oracle (exact argmin over candidates that carry the reference's exact T
+roundings) (i) index-match rate, (ii) for mismatches the oracle error of our choice is within (1 + 1e-3) of the oracle's
+minimum, (iii) the returned clip values are bit-exactly org * (1 - i/20) rounded to T for the chosen index."""
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from _util import DT, load_cases, t
+
+pytestmark = pytest.mark.gpu
+dev = torch.device("cuda:0")
+
+
+def _grid_values(w, G, dt):
+    co = w.shape[0]
+    wg = w.reshape(co, -1, G)
+    mx, mn = wg.amax(-1).float(), wg.amin(-1).float()
+    fac = torch.tensor([float(np.float32(1 - i / 20)) for i in range(10)])
+    return (mx[..., None] * fac).to(dt), (mn[..., None] * fac).to(dt)   # [co, ng, 10]
+
+
+def _check(w, x_sampled, G, qt, bmax, bmin, idx, err, dt, min_match, rel=1e-3):
+    r = oracle.auto_2clip(w, x_sampled, G, 2, qt, want_all_err=True)
+    idx = idx.cpu().long()
+    co, ng = idx.shape
+    cmax, cmin = _grid_values(w, G, dt)
+    valid = idx >= 0
+    assert bool((valid == (r["idx"] >= 0)).all())
+    ii = idx.clamp(min=0)
+    # (iii) values are exactly the grid values of the chosen index (org value when nothing won)
+    exp_max = torch.where(valid, cmax.gather(-1, (ii // 10)[..., None]).squeeze(-1), cmax[..., 0])
+    exp_min = torch.where(valid, cmin.gather(-1, (ii % 10)[..., None]).squeeze(-1), cmin[..., 0])
+    assert torch.equal(bmax.cpu().reshape(co, ng).float(), exp_max.float())
+    assert torch.equal(bmin.cpu().reshape(co, ng).float(), exp_min.float())
+    # (i) index match, (ii) near-optimality of mismatches under the oracle's error
+    match = (idx == r["idx"].long())[valid].float().mean().item()
+    e_ours = r["all_err"].gather(-1, ii[..., None]).squeeze(-1)
+    ok = e_ours <= r["err"] * (1 + rel) + 1e-30
+    assert bool(ok[valid].all()), float((e_ours / r["err"])[valid].max())
+    assert match >= min_match, match
+    # our fp32 error of the winner agrees with the oracle's double error of the same candidate
+    e = err.cpu().double()
+    assert bool(((e - e_ours).abs() <= 2e-3 * e_ours + 1e-20)[valid].all())
+    return match
+
+
+def test_autoclip_golden_cases():
+    from bitdistiller_b200.autoclip import auto_2clip_layer
+    n = 0
+    for meta, c in load_cases("autoclip"):
+        dname, qt, G = meta[0], meta[1], int(meta[2])
+        dt = DT[dname]
+        w, x = t(c["w"], dt), t(c["x"], dt)
+        q_config = {"zero_point": True, "q_group_size": G, "quant_type": qt}
+        bmax, bmin, idx, err = auto_2clip_layer(w.to(dev), x.to(dev), 2, q_config, return_info=True)
+        assert bmax.shape == (w.shape[0], w.shape[1] // G, 1) and bmax.dtype == dt
+        xs = x[0::x.shape[0] // 512]
+        m = _check(w, xs, G, qt, bmax, bmin, idx, err, dt, min_match=0.985)
+        # against the reference's own (T-dtype, noise-limited) choice: its candidate must be close to ours in oracle error
+        n += 1
+        print(meta, "index match vs oracle", m)
+    assert n == 8
+
+
+@pytest.mark.parametrize("qt", ["int", "nf3"])
+def test_autoclip_llama_slice_bf16(qt):
+    """A [128, 1024] bf16 slice with outlier-channel activations (BASELINE config 4 generator), 512 tokens."""
+    from bitdistiller_b200.autoclip import auto_2clip_layer
+    g = torch.Generator().manual_seed(17)
+    w = (torch.randn(128, 1024, generator=g) * 0.02).to(torch.bfloat16)
+    ch = torch.exp(torch.randn(1024, generator=g) * 0.5)
+    x = (torch.randn(1024, 1024, generator=g) * ch).to(torch.bfloat16)   # 1024 tokens -> stride 2 -> 512 sampled
+    q_config = {"zero_point": True, "q_group_size": 128, "quant_type": qt}
+    bmax, bmin, idx, err = auto_2clip_layer(w.to(dev), x.to(dev), 2, q_config, return_info=True)
+    _check(w, x[0::2], 128, qt, bmax, bmin, idx, err, torch.bfloat16, min_match=0.985)
+
+
+def test_autoclip_api_and_errors():
+    from bitdistiller_b200 import autoclip as A
+    w = torch.randn(64, 256, device=dev).bfloat16() * 0.02
+    x = torch.randn(512, 256, device=dev).bfloat16()
+    with pytest.raises(ValueError):
+        A.auto_2clip_layer(w, x, 2, {"zero_point": True, "q_group_size": 128, "quant_type": "fp4"})
+    a, b = A.auto_clip_layer(w, x, 2, {"zero_point": True, "q_group_size": 128, "quant_type": "int"})
+    assert a.shape == (64, 2, 1) and b.shape == (64, 2, 1)
+    # auto_clip_block skips q/k projections and returns (name, max, min) triples that apply_clip accepts
+    blk = torch.nn.Module()
+    blk.q_proj = torch.nn.Linear(256, 64, bias=False, dtype=torch.bfloat16)
+    blk.v_proj = torch.nn.Linear(256, 64, bias=False, dtype=torch.bfloat16)
+    feats = {"q_proj": x.cpu(), "v_proj": x.cpu()}
+    res = A.auto_clip_block(blk, 2, {"zero_point": True, "q_group_size": 128, "quant_type": "int"}, feats)
+    assert [r[0] for r in res] == ["v_proj"]
+    w0 = blk.v_proj.weight.data.clone()
+    A.apply_clip(blk, res)
+    wc = blk.v_proj.weight.data
+    ref = oracle.apply_clip(w0.cpu(), res[0][2].cpu(), res[0][1].cpu())
+    assert torch.equal(wc.cpu().float(), ref.float())
