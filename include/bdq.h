@@ -122,6 +122,17 @@ int bdq_gemv_w2(const void* x, const int32_t* qweight, const void* scales, const
                 int64_t B, int64_t IC, int64_t OC, int group, int flags, bdq_stream_t stream);
 
 /*
+ * Packed 2-bit prefill GEMM: out[m, oc] = fp16( sum_k x[m,k] * fp16(scales[oc,k/G] * (code[oc,k] - zero[oc,k/G])) ),
+ * fp32 accumulation in tensor memory (tcgen05.mma, TMA-fed activations, in-register dequant of the packed weights).
+ * Replaces quant_matmul_v2 (quantization/triton_kernels.py:102-134) and gemm_forward_cuda (pybind.cpp:12; the
+ * reference's CUDA GEMM is 4-bit only).  Operands are the row-major tensors WQLinear holds (qmodule.py:62-66) -- NOT the
+ * transposed copies the reference builds per call (qmodule.py:154-158).  x [M, IC] fp16, out [M, OC] fp16.
+ * Tensor-core path: group in {64, 128}, IC % 128 == 0, OC % 256 == 0; other shapes fall back to bdq_gemv_w2 row blocks.
+ */
+int bdq_gemm_w2(const void* x, const int32_t* qweight, const void* scales, const int32_t* qzeros, void* out, int64_t M,
+                int64_t IC, int64_t OC, int group, bdq_stream_t stream);
+
+/*
  * Two-sided clip-ratio grid search = auto_2clip_layer (quantization/autoclip.py:13-83), all candidates of all
  * (output channel, group) pairs in one launch.  w [co, ci] (T, row-major); x = the calibration activations
  * [n_tok, ci] of the same dtype with a row stride of x_row_stride elements (the reference's token sub-sampling

@@ -1,0 +1,88 @@
+"""GPU parity tests for the packed int2 prefill GEMM (tcgen05 path), through the C ABI.
+Bar (BASELINE.json north_star): GEMM outputs within rtol 1e-2 of the reference math (dequant rounded to fp16, fp32
+accumulate, fp16 store = quant_matmul_kernel, triton_kernels.py:89-93)."""
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from _util import make_weight
+
+pytestmark = pytest.mark.gpu
+dev = torch.device("cuda:0")
+
+
+def _packed_layer(oc, ic, seed, G=128):
+    from bitdistiller_b200 import quantizer as Q
+    from bitdistiller_b200.qmodule import pack_wq
+    w = make_weight("randn", oc, ic, torch.float16, seed).to(dev)
+    dq, s, z, _ = Q.int_fakequant(w, 2, G, 0, want_scale_zp=True)
+    return pack_wq(dq, s.view(oc, -1), z.view(oc, -1), 2, G), dq
+
+
+def _ref_gpu(x, qw, qz, qs, G):
+    """dequant rounded to fp16 then fp32 matmul, on the GPU (cuBLAS fp32) -- the full-size check."""
+    oc, wpr = qw.shape
+    ic = wpr * 16
+    sh = (torch.arange(16, device=dev, dtype=torch.int32) * 2)
+    codes = ((qw[:, :, None] >> sh) & 3).reshape(oc, ic).float()
+    ng = ic // G
+    zz = ((qz[:, :, None] >> sh) & 3).reshape(oc, -1)[:, :ng].float()
+    dqw = (qs[:, :ng].float().repeat_interleave(G, 1) * (codes - zz.repeat_interleave(G, 1))).half()
+    return (x.float() @ dqw.float().T), dqw
+
+
+def _check(out, ref, x, dqw):
+    out, ref = out.double(), ref.double()
+    scale = (x.double().abs() @ dqw.double().abs().T)
+    tol = 1e-2 * ref.abs() + 2e-3 * scale / np.sqrt(x.shape[1]) + 1e-6
+    bad = (out - ref).abs() > tol
+    assert not bool(bad.any()), (int(bad.sum()), float((out - ref).abs().max()))
+    assert float((out - ref).norm() / ref.norm()) < 1e-3
+
+
+@pytest.mark.parametrize("m,oc,ic,G", [(128, 256, 128, 128), (256, 512, 1024, 128), (2048, 4096, 4096, 128),
+                                       (200, 256, 11008, 128), (77, 1024, 4096, 128), (384, 512, 2048, 64)])
+def test_gemm_w2_tcgen05_vs_reference_math(m, oc, ic, G):
+    from bitdistiller_b200.triton_kernels import gemm_w2
+    (qw, qz, qs), dq = _packed_layer(oc, ic, 5, G)
+    x = torch.randn(m, ic, generator=torch.Generator().manual_seed(m)).to(torch.float16).to(dev)
+    out = gemm_w2(x, qw, qs, qz, G)
+    torch.cuda.synchronize()
+    assert out.shape == (m, oc) and out.dtype == torch.float16
+    ref, dqw = _ref_gpu(x, qw, qz, qs, G)
+    _check(out, ref, x, dqw)
+    # a slab against the CPU oracle (double accumulation of the fp16-rounded dequant)
+    ms, os_ = min(m, 16), min(oc, 64)
+    orc = oracle.wq_matmul(x[:ms].cpu(), qw[:os_].cpu(), qz[:os_].cpu(), qs[:os_].cpu(), G, 2, dequant_fp16=True)
+    _check(out[:ms, :os_].cpu(), orc, x[:ms].cpu(), dqw[:os_].cpu())
+
+
+def test_wqlinear_prefill_and_quant_matmul_v2_convention():
+    from bitdistiller_b200.qmodule import WQLinear
+    from bitdistiller_b200.quantizer import pseudo_quantize_tensor
+    from bitdistiller_b200.triton_kernels import quant_matmul_v2
+    lin = torch.nn.Linear(1024, 512, bias=True, dtype=torch.float16, device=dev)
+    lin.weight.data = make_weight("randn", 512, 1024, torch.float16, 9).to(dev)
+    lin.weight.data, s, z = pseudo_quantize_tensor(lin.weight.data, n_bit=2, q_group_size=128, get_scale_zp=True)
+    ql = WQLinear.from_linear(lin, 2, 128, False, s, z)
+    x = torch.randn(2, 40, 1024, device=dev, dtype=torch.float16)
+    with torch.no_grad():
+        y = ql(x)
+        ref = torch.nn.functional.linear(x.float(), lin.weight.data.float(), lin.bias.float())
+    assert y.shape == (2, 40, 512)
+    assert float((y.float() - ref).norm() / ref.norm()) < 2e-3
+    # the reference's transposed calling convention (qmodule.py:154-166)
+    y2 = quant_matmul_v2(x.reshape(-1, 1024), ql.qweight.T.contiguous(), ql.qzeros.T.contiguous(), ql.scales.T.contiguous(),
+                         M=80, N=512, K=1024, pack_num=16, group_size=128, w_bit=2, offset=3)
+    assert torch.equal(y2 + ql.bias, y.reshape(-1, 512))
+
+
+def test_gemm_w2_fallback_shapes():
+    """OC not a multiple of 256 takes the GEMV row-block fallback and still matches."""
+    from bitdistiller_b200.triton_kernels import gemm_w2
+    (qw, qz, qs), dq = _packed_layer(64, 512, 3)
+    x = torch.randn(20, 512, generator=torch.Generator().manual_seed(1)).to(torch.float16).to(dev)
+    out = gemm_w2(x, qw, qs, qz, 128)
+    ref, dqw = _ref_gpu(x, qw, qz, qs, 128)
+    _check(out, ref, x, dqw)

@@ -1,0 +1,43 @@
+"""Prefill GEMM micro-benchmark (BASELINE config 5b): Qwen3-8B packed int2-g128, M = 2048 tokens."""
+import os, sys
+import torch
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from bitdistiller_b200 import quantizer as Q  # noqa: E402
+from bitdistiller_b200.qmodule import pack_wq  # noqa: E402
+from bitdistiller_b200.triton_kernels import gemm_w2  # noqa: E402
+
+dev = torch.device("cuda:0")
+M = int(sys.argv[1]) if len(sys.argv) > 1 else 2048
+tot_f, tot_t = 0.0, 0.0
+for name, oc, ic, mult in [("q/o_proj", 4096, 4096, 2), ("k/v_proj", 1024, 4096, 2), ("gate/up_proj", 12288, 4096, 2), ("down_proj", 4096, 12288, 1)]:
+    w = (torch.randn(oc, ic, device=dev) * 0.02).half()
+    dq, s, z, _ = Q.int_fakequant(w, 2, 128, 0, want_scale_zp=True)
+    qw, qz, qs = pack_wq(dq, s.view(oc, -1), z.view(oc, -1), 2, 128)
+    x = torch.randn(M, ic, device=dev).half()
+    for _ in range(3):
+        gemm_w2(x, qw, qs, qz, 128)
+    torch.cuda.synchronize()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(11)]
+    ev[0].record()
+    for i in range(10):
+        gemm_w2(x, qw, qs, qz, 128)
+        ev[i + 1].record()
+    torch.cuda.synchronize()
+    ts = sorted(ev[i].elapsed_time(ev[i + 1]) for i in range(10))
+    t = ts[5] * 1e-3
+    f = 2.0 * M * oc * ic
+    for _ in range(3):
+        torch.matmul(x, dq.T)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(10):
+        torch.matmul(x, dq.T)
+    e1.record()
+    torch.cuda.synchronize()
+    tc = e0.elapsed_time(e1) * 1e-4
+    print(f"M={M} {name:13s} [{oc}x{ic}] {t*1e6:8.1f} us  {f/t/1e12:7.1f} TFLOP/s  ({f/t/1e12/1400.3*100:5.1f}% of measured sustained bf16 peak)"
+          f"   cuBLAS fp16 dense on dequantised W: {tc*1e6:8.1f} us {f/tc/1e12:7.1f} TFLOP/s")
+    tot_f += f * mult
+    tot_t += t * mult
+print(f"Qwen3-8B prefill, all 36 layers' linears, M={M}: {tot_t*36*1e3:.2f} ms  {tot_f*36/(tot_t*36)/1e12:.1f} TFLOP/s")
