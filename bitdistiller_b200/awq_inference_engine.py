@@ -13,7 +13,10 @@ def _check_fp16(*ts):
             raise TypeError(f"expected a float16 tensor (the reference kernels are fp16-only), got {t.dtype}")
 
 
-def gemv_forward_cuda(in_feats, kernel, scaling_factors, zeros, w_bit, group_size, pdl=False):
+GEMV_PDL, GEMV_CTAS1, GEMV_RING = 1, 2, 4   # include/bdq.h
+
+
+def gemv_forward_cuda(in_feats, kernel, scaling_factors, zeros, w_bit, group_size, pdl=False, flags=0):
     """[B, IC] fp16 x packed [OC, IC/16] int32 -> [B, OC] fp16.  Unlike the reference, unsupported (w_bit, group_size)
     raise instead of returning uninitialised memory (gemv_cuda.cu:316-344)."""
     L.require_cuda(in_feats, kernel, scaling_factors, zeros)
@@ -29,9 +32,41 @@ def gemv_forward_cuda(in_feats, kernel, scaling_factors, zeros, w_bit, group_siz
     out = torch.empty((B, OC), dtype=torch.float16, device=x.device)
     with torch.cuda.device(x.device):
         rc = L.lib().bdq_gemv_w2(L.ptr(x), L.ptr(kernel), L.ptr(scaling_factors), L.ptr(zeros), L.ptr(out), L.i64(B),
-                                 L.i64(IC), L.i64(OC), int(group_size), 1 if pdl else 0, L.stream_ptr(x.device))
+                                 L.i64(IC), L.i64(OC), int(group_size), int(flags) | (GEMV_PDL if pdl else 0),
+                                 L.stream_ptr(x.device))
     L.check(rc, "bdq_gemv_w2")
     return out
+
+
+def gemv_multi_forward_cuda(in_feats, kernels, scaling_factors, zeros, group_size, pdl=False, flags=0, outs=None,
+                            prefetch=()):
+    """Batch-1 decode GEMV of up to 4 packed matrices sharing `in_feats` [1, IC] in ONE launch (bdq_gemv_w2_multi): the
+    fused q/k/v and gate/up projections of inference/modules/fused_attn.py:304-340 / fused_mlp.py:44-114 without
+    concatenating the packed tensors.  `prefetch`: up to 4 tensors (the packed weights of the next launch of the decode
+    chain) to pull into L2 while this launch computes.  Returns a list of [1, OC_i] fp16 tensors."""
+    import ctypes
+    n = len(kernels)
+    L.require_cuda(in_feats, *kernels, *scaling_factors, *zeros)
+    _check_fp16(in_feats, *scaling_factors)
+    x = in_feats.contiguous()
+    if x.numel() != x.shape[-1]:
+        raise ValueError("gemv_multi_forward_cuda is the batch-1 decode path: in_feats must hold one row")
+    IC = x.shape[-1]
+    for k, s, z in zip(kernels, scaling_factors, zeros):
+        assert k.is_contiguous() and s.is_contiguous() and z.is_contiguous() and k.shape[1] * 16 == IC
+    if outs is None:
+        outs = [torch.empty((1, k.shape[0]), dtype=torch.float16, device=x.device) for k in kernels]
+    arr = lambda ts: (ctypes.c_void_p * n)(*[t.data_ptr() for t in ts])
+    oc = (ctypes.c_int64 * n)(*[k.shape[0] for k in kernels])
+    npf = len(prefetch)
+    pf_ptr = (ctypes.c_void_p * max(npf, 1))(*[t.data_ptr() for t in prefetch])
+    pf_len = (ctypes.c_int64 * max(npf, 1))(*[t.numel() * t.element_size() for t in prefetch])
+    with torch.cuda.device(x.device):
+        rc = L.lib().bdq_gemv_w2_multi(L.ptr(x), n, arr(kernels), arr(scaling_factors), arr(zeros), arr(outs), oc,
+                                       L.i64(IC), int(group_size), int(flags) | (GEMV_PDL if pdl else 0),
+                                       npf, pf_ptr, pf_len, L.stream_ptr(x.device))
+    L.check(rc, "bdq_gemv_w2_multi")
+    return outs
 
 
 def gemm_forward_cuda(in_feats, kernel, scaling_factors, zeros, group_size, split_k_iters, w_bit=2):

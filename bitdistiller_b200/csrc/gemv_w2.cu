@@ -332,6 +332,10 @@ __global__ void __launch_bounds__(256) gemv_w2_generic_kernel(const __half* __re
 
 using namespace bdq;
 
+int bdq_gemv_w2_stream_launch(const void* x, int nmat, const int32_t* const* qweight, const void* const* scales,
+                              const int32_t* const* qzeros, void* const* out, const int64_t* OC, int64_t IC, int flags,
+                              cudaStream_t st, int n_prefetch, const void* const* prefetch, const int64_t* prefetch_bytes);
+
 extern "C" int bdq_gemv_w2(const void* x, const int32_t* qweight, const void* scales, const int32_t* qzeros, void* out,
                            int64_t B, int64_t IC, int64_t OC, int group, int flags, bdq_stream_t stream) {
     if (B < 0 || IC <= 0 || OC <= 0 || group <= 0 || IC % group != 0 || IC % 16 != 0 || group % 16 != 0) {
@@ -345,6 +349,15 @@ extern "C" int bdq_gemv_w2(const void* x, const int32_t* qweight, const void* sc
     if (!x || !qweight || !scales || !qzeros || !out) { set_error("null tensor pointer"); return BDQ_ERR_SHAPE; }
     if (IC > (1 << 20) || OC > (1 << 24)) { set_error("gemv_w2: shape too large"); return BDQ_ERR_SHAPE; }
     cudaStream_t st = (cudaStream_t)stream;
+    if (B == 1 && group == 128 && !(flags & BDQ_GEMV_RING)) {   // batch 1: register-streaming kernel (gemv_w2_stream.cu)
+        const int32_t* qw1[1] = {qweight};
+        const void* sc1[1] = {scales};
+        const int32_t* qz1[1] = {qzeros};
+        void* out1[1] = {out};
+        const int64_t oc1[1] = {OC};
+        const int rc = bdq_gemv_w2_stream_launch(x, 1, qw1, sc1, qz1, out1, oc1, IC, flags, st, 0, nullptr, nullptr);
+        if (rc != BDQ_ERR_UNSUPPORTED) return rc;
+    }
     const bool fast = group == 128 && OC % 16 == 0 && ((uintptr_t)x % 16 == 0) && ((uintptr_t)qweight % 16 == 0) &&
                       ((uintptr_t)scales % 16 == 0) && ((uintptr_t)qzeros % 16 == 0);
     if (!fast) {

@@ -118,8 +118,28 @@ int bdq_pack_wq(const void* w_dq, const void* scales, const void* zeros, int32_t
  * overlaps the tail of the previous kernel on the stream; x is read only after the dependency resolves).
  */
 #define BDQ_GEMV_PDL 1
+#define BDQ_GEMV_CTAS1 2 /* batch-1 streaming kernel: one CTA per SM instead of two (tuning knob) */
+#define BDQ_GEMV_RING 4  /* force the shared-memory ring kernel (the batch 2..8 path) also for batch 1 */
+#define BDQ_GEMV_PROF 8  /* dev tool: record %globaltimer phase marks into the buffer given to bdq_gemv_set_prof */
+int bdq_gemv_set_prof(void* device_buf_u64, int64_t capacity_u64);
 int bdq_gemv_w2(const void* x, const int32_t* qweight, const void* scales, const int32_t* qzeros, void* out,
                 int64_t B, int64_t IC, int64_t OC, int group, int flags, bdq_stream_t stream);
+
+/*
+ * Batch-1 decode GEMV of up to 4 packed matrices that share one activation vector, in ONE launch: the fused q/k/v
+ * projection and the fused gate/up projection of the reference's decode modules
+ * (inference/modules/fused_attn.py:304-340 concatenates q,k,v into one WQLinear; inference/modules/fused_mlp.py:44-114
+ * issues gate and up back to back).  x [IC] fp16; for i < nmat: qweight[i] / scales[i] / qzeros[i] as produced by
+ * bdq_pack_wq for a [OC[i], IC] weight, out[i] [OC[i]] fp16.  The pointer arrays are HOST arrays of device pointers.
+ * group 128, OC[i] % 16 == 0 take the fused kernel; anything else falls back to one bdq_gemv_w2 launch per matrix.
+ * Prefetch hint (optional, n_prefetch 0..4): prefetch[i] / prefetch_bytes[i] name device buffers -- normally the
+ * qweight tensors of the NEXT launch of the decode chain -- that this launch pulls into L2 with
+ * cp.async.bulk.prefetch.L2 while it computes, so HBM keeps streaming across the launch boundary.  Purely a hint:
+ * results do not depend on it.
+ */
+int bdq_gemv_w2_multi(const void* x, int nmat, const int32_t* const* qweight, const void* const* scales,
+                      const int32_t* const* qzeros, void* const* out, const int64_t* OC, int64_t IC, int group, int flags,
+                      int n_prefetch, const void* const* prefetch, const int64_t* prefetch_bytes, bdq_stream_t stream);
 
 /*
  * Packed 2-bit prefill GEMM: out[m, oc] = fp16( sum_k x[m,k] * fp16(scales[oc,k/G] * (code[oc,k] - zero[oc,k/G])) ),

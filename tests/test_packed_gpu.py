@@ -90,6 +90,57 @@ def test_gemv_w2_vs_oracle(oc, ic, pdl):
     assert float((out.float() - full).norm() / full.norm()) < 2e-3
 
 
+@pytest.mark.parametrize("oc,ic,flags", [(4096, 4096, 2), (4096, 4096, 4), (4096, 12288, 6), (48, 2176, 0), (48, 2176, 2),
+                                         (16, 128, 1), (1040, 640, 3)])
+def test_gemv_w2_batch1_variants(oc, ic, flags):
+    """Batch 1 through both kernels: streaming (flags 0/1), one CTA per SM (2), the ring kernel (4); ragged shapes
+    (17 groups, 5 groups, a single group)."""
+    from bitdistiller_b200 import awq_inference_engine as E
+    (qw, qz, qs), dq = _packed_layer(oc, ic, 100 + flags)
+    x = torch.randn(1, ic, generator=torch.Generator().manual_seed(oc + ic)).to(torch.float16).to(dev)
+    out = E.gemv_forward_cuda(x, qw, qs, qz, 2, 128, flags=flags)
+    sub = slice(0, min(oc, 256))
+    ref = oracle.wq_matmul(x.cpu(), qw[sub].cpu(), qz[sub].cpu(), qs[sub].cpu(), 128, 2)
+    _check_gemv(out[:, sub], ref, x, dq[sub])
+    full = (x.float() @ dq.float().T)
+    assert float((out.float() - full).norm() / full.norm()) < 2e-3
+
+
+@pytest.mark.parametrize("ocs,ic", [((4096, 1024, 1024), 4096), ((12288, 12288), 4096), ((4096, 48, 16, 1024), 11008)])
+@pytest.mark.parametrize("pdl", [False, True])
+def test_gemv_w2_multi(ocs, ic, pdl):
+    """Fused q/k/v and gate/up launches: every matrix's output equals its stand-alone GEMV bit for bit (same kernel,
+    same summation order) and the oracle within rtol 1e-2."""
+    from bitdistiller_b200 import awq_inference_engine as E
+    layers = [_packed_layer(oc, ic, 200 + i) for i, oc in enumerate(ocs)]
+    x = torch.randn(1, ic, generator=torch.Generator().manual_seed(9)).to(torch.float16).to(dev)
+    outs = E.gemv_multi_forward_cuda(x, [l[0][0] for l in layers], [l[0][2] for l in layers], [l[0][1] for l in layers],
+                                     128, pdl=pdl, prefetch=[l[0][0] for l in layers[:2]] if pdl else ())
+    for ((qw, qz, qs), dq), out in zip(layers, outs):
+        single = E.gemv_forward_cuda(x, qw, qs, qz, 2, 128)
+        assert torch.equal(out, single)
+        sub = slice(0, min(qw.shape[0], 128))
+        ref = oracle.wq_matmul(x.cpu(), qw[sub].cpu(), qz[sub].cpu(), qs[sub].cpu(), 128, 2)
+        _check_gemv(out[:, sub], ref, x, dq[sub])
+
+
+def test_gemv_w2_pdl_chain_dependent():
+    """A dependent chain under programmatic dependent launch: each GEMV reads the previous one's output (x is loaded
+    only after griddepcontrol.wait), results equal the plain-launch chain bit for bit."""
+    from bitdistiller_b200 import awq_inference_engine as E
+    (qw, qz, qs), _ = _packed_layer(4096, 4096, 77)
+    x0 = torch.randn(1, 4096, generator=torch.Generator().manual_seed(3)).to(torch.float16).to(dev)
+
+    def chain(pdl):
+        x = x0
+        for _ in range(6):
+            x = E.gemv_forward_cuda(x, qw, qs, qz, 2, 128, pdl=pdl)
+            x = x  # [1, 4096] feeds the next launch
+        return x
+    a, b = chain(False), chain(True)
+    assert torch.isfinite(a).all() and torch.equal(a, b)
+
+
 @pytest.mark.parametrize("B", [2, 5, 8, 11])
 def test_gemv_w2_batched(B):
     from bitdistiller_b200 import awq_inference_engine as E

@@ -1,0 +1,79 @@
+"""Dev tool: %globaltimer phase timeline of the batch-1 streaming GEMV inside a CUDA graph (BDQ_GEMV_PROF).
+usage: python tools/gemv_timeline.py [shape=gate|q|down|layer] [flags]"""
+import ctypes
+import os
+import sys
+
+import numpy as np
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from bitdistiller_b200 import _lib as L  # noqa: E402
+from tools.bench_gemv import QWEN3_8B, build, run, ctypes_stream  # noqa: E402
+
+
+def main():
+    dev = torch.device("cuda:0")
+    which = sys.argv[1] if len(sys.argv) > 1 else "gate"
+    flags = int(sys.argv[2]) if len(sys.argv) > 2 else 1
+    pre = len(sys.argv) > 3 and sys.argv[3] == "pf"
+    ops = build(dev, layers=36)
+    fused = False
+    if which == "layer":
+        sel, fused = ops[: 7 * 12], True
+    else:
+        name = {"gate": "gate_proj", "q": "q_proj", "down": "down_proj", "k": "k_proj"}[which]
+        idx = [i for i, s in enumerate(QWEN3_8B) if s[0] == name][0]
+        sel = ops[idx::7][:24]
+    lib = L.lib()
+    cap = 64 * 1024 * 1024 // 8
+    prof = torch.zeros(cap, dtype=torch.int64, device=dev)
+    s = torch.cuda.Stream(dev)
+    with torch.cuda.stream(s):
+        run(sel, flags, ctypes_stream(s), fused, pre)
+        torch.cuda.synchronize()
+        lib.bdq_gemv_set_prof(ctypes.c_void_p(prof.data_ptr()), ctypes.c_int64(cap))
+        gr = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gr, stream=s):
+            run(sel, flags | 8, ctypes_stream(s), fused, pre)
+        lib.bdq_gemv_set_prof(None, ctypes.c_int64(0))
+    for _ in range(3):
+        gr.replay()
+    torch.cuda.synchronize()
+    p = prof.cpu().numpy().astype(np.int64)
+    nsm = torch.cuda.get_device_properties(dev).multi_processor_count
+    grid_of = lambda rb: min(nsm * (1 if flags & 2 else 2), rb)
+    # slabs in launch order
+    off, launches = 0, []
+    i = 0
+    while i < len(sel):
+        n = 1
+        if fused:
+            nm = QWEN3_8B[i % 7][0]
+            n = 3 if nm == "q_proj" else (2 if nm == "gate_proj" else 1)
+        rb = sum(o[7] for o in sel[i:i + n]) // 16
+        g = grid_of(rb)
+        launches.append((QWEN3_8B[i % 7][0] if fused else which, g, p[off:off + g * 8 * 16].reshape(g, 8, 16)))
+        off += g * 8 * 16
+        i += n
+    t0 = min(int(a[:, :, 0].min()) for _, _, a in launches)
+    prev_end = None
+    print("launch name      grid | first start, median start | median issue-done, wait-done, x-staged | median per-mark "
+          "deltas ... | last end  (us, relative to the first launch; gaps vs previous launch's last end)")
+    for li, (nm, g, a) in enumerate(launches):
+        a = a.astype(np.float64)
+        valid = a > 0
+        a = np.where(valid, (a - t0) * 1e-3, np.nan)
+        st = a[:, :, 0]
+        last = np.nanmax(a, axis=2)
+        med = lambda v: float(np.nanmedian(v))
+        marks = [med(a[:, :, k] - a[:, :, 0]) for k in range(1, 16) if np.isfinite(a[:, :, k]).any()]
+        end = float(np.nanmax(last))
+        gap = "" if prev_end is None else f" start-prev_end {float(np.nanmin(st)) - prev_end:+6.2f} wait_rel-prev_end {med(a[:, :, 2]) - prev_end:+6.2f}"
+        print(f"{li:3d} {nm:10s} {g:4d} | {float(np.nanmin(st)):8.2f} {med(st):8.2f} | dur(max) {end - float(np.nanmin(st)):6.2f} | "
+              + " ".join(f"{m:5.2f}" for m in marks) + f" | end {end:8.2f}{gap}")
+        prev_end = end
+
+
+if __name__ == "__main__":
+    main()
