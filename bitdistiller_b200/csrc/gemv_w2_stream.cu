@@ -9,8 +9,8 @@
 //     will consume itself (one quantisation group of channels g and g+8) straight into registers with LDG.256, kDepth
 //     items deep.  (A per-warp cp.async ring was measured too: with one row per 4 lanes every LDGSTS.128 costs 32
 //     shared-memory wavefronts instead of 4 and the MIO pipe becomes the bound -- profiles/r01_gemv_notes.md);
-//   * two CTAs (16 warps) per SM: a warp alone issues one instruction per ~4 cycles (LOP3 -> HMMA dependencies), four
-//     warps per scheduler are needed to fill the ALU pipe;
+//   * two CTAs (16 warps) per SM: a warp alone issues one instruction per ~4 cycles (LOP3 -> MMA dependencies), four
+//     warps per scheduler are needed to fill the pipes;
 //   * the weights of the NEXT launch can be handed in as a prefetch hint: one lane per CTA issues
 //     cp.async.bulk.prefetch.L2 for its slice at kernel start, so HBM keeps streaming across the launch boundary and
 //     the next launch finds its weights in L2 (every byte still crosses HBM exactly once per token);
@@ -18,14 +18,20 @@
 //     x is read only after the dependency resolves);
 //   * x is staged per warp (each warp only needs the K windows it owns), so the only CTA-wide barrier is the split-K
 //     reduction at the end of a 16-channel block;
-//   * 2-bit codes become fp16 with one LOP3 per two codes ((word & mask) | exponent = K + code, K in
-//     {1024,256,64,16,4}) plus one shift per word; the dot products run on the tensor pipe
-//     (mma.sync.m16n8k16, fp32 accumulate).  With batch 1 the N dimension of the MMA is used to keep the four
-//     quantisation groups of a 512-wide K window apart: lane t of a quad holds group t of the window and the B
-//     operand column n carries x only for group n (zero elsewhere), so D[row][n] is the group-n partial sum and the
-//     scale / zero-point fix-up runs once per 4 groups instead of once per group:
-//         out[oc] += s[oc,g] * (D[oc][g] - sum_k K(k) x[k] - z[oc,g] * sum_k x[k])
-//   * the x-only sums are computed once per warp while x is staged in extraction order.
+//   * the dot products run on the INT8 tensor pipe (mma.sync.m16n8k32.s32.u8.s8, 8 cycles per scheduler on B200,
+//     measured) with NO per-code extraction: A = word & (0x03030303 << 2i) is (code << 2i) for digit i of every byte,
+//     one LOP3 per four codes, no shift; digit i accumulates in its own int32 tile and the 4^-i factors are applied in
+//     the fp32 fix-up (all intermediate values are integers below 2^24, i.e. exact).  An fp16 mma.sync formulation
+//     ((word & mask) | exponent, 9 ALU ops per 16 codes) was measured first and was ALU-pipe bound at ~0.7x the HBM rate;
+//   * x becomes block fixed point per quantisation group while it is staged: q = rint(x / unit) with |q| <= 8192 and
+//     unit a power of two from the group's largest magnitude, split into two int8 limbs q = 256 hi + lo (error
+//     <= 2^-14 of the group maximum per element, below the fp16 rounding of x itself for the elements that matter);
+//   * with batch 1 the N dimension of the MMA keeps the four quantisation groups of a 512-wide K window AND the two
+//     limbs apart: lane t of a quad holds group t, B column 2*group + limb carries that limb of x for the k rows of
+//     group `group` only (zero elsewhere), so every lane ends up with the (hi, lo) sums of its own group and the
+//     scale / zero-point fix-up runs once per group per lane:
+//         out[oc] += s[oc,g] * unit[g] * (256 * HI + LO - z[oc,g] * sum_k q[k])
+//   * non-finite activations make the group's unit NaN, so the affected outputs are NaN (not silently finite).
 #include "bdq_common.cuh"
 
 namespace bdq {
@@ -33,11 +39,12 @@ namespace bdq {
 constexpr int kSThreads = 256;
 constexpr int kSWarps = 8;
 constexpr int kDepth = 3;              // items (16 channels x 512 input channels = 2 KB) in flight per warp
-constexpr int kGrpStride = 272;        // 256 B of permuted x per group + 16 B so the 4 active lanes hit distinct banks
-constexpr int kWinStride = 1152;      // 4 groups + (Kx, Sx) of the 4 groups at +1088, padded to a multiple of 128
-constexpr int kMetaOff = 4 * kGrpStride;
-constexpr int kZeroBytes = 384;        // per-warp zero block read by the lanes whose B column is empty
+constexpr int kSlotStride = 144;       // 128 B of int8 x limbs per (group, limb) + 16 B: the 8 active lanes hit distinct banks
+constexpr int kMetaOff = 8 * kSlotStride;   // (unit, sum of quantised x) per group, 4 x float2
+constexpr int kWinStride = 1280;       // 8 slots + meta, padded to a multiple of 128
+constexpr int kZeroBytes = 256;        // per-warp zero block read by the lanes whose B column is empty
 constexpr int kMaxMats = 4;
+constexpr int kRedSlots = 8;           // finished 16-channel blocks parked per CTA between split-K reductions
 
 struct GemvMats {
     const uint8_t* qw[kMaxMats];
@@ -51,37 +58,14 @@ struct GemvMats {
 
 struct ItemBuf {
     U8 a, b;              // packed codes: channel g / g+8, one group (128 codes) each
-    uint32_t sa, sb;      // two fp16 scales each: channel g / g+8, groups 2(t&1), 2(t&1)+1 of the window
-    uint32_t za, zb;      // the zero-point words holding those groups
+    uint32_t sa, sb;      // fp16 scale of this lane's group: channel g / g+8
+    uint32_t za, zb;      // the zero-point words holding that group
 };
 
-__device__ __forceinline__ uint32_t lop_and_or_s(uint32_t a, uint32_t b, uint32_t c) {
-    uint32_t r;
-    asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(r) : "r"(a), "r"(b), "r"(c));   // (a & b) | c
-    return r;
-}
-
-// additive offset of extraction e: codes e and e+8 of a word come out as (K + code)
-__host__ __device__ constexpr float ext_ks(int e) {
-    return (e == 0 || e == 5) ? 1024.f : (e == 1 || e == 6) ? 256.f : (e == 2 || e == 7) ? 64.f : (e == 3) ? 16.f : 4.f;
-}
-
-// h[e] = half2(K_e + code[e], K_e + code[e + 8]), e = 0..7: 8 LOP3 + 1 shift for 16 codes
-__device__ __forceinline__ void extract16s(uint32_t v, uint32_t* h) {
-    const uint32_t v1 = v >> 10;
-    h[0] = lop_and_or_s(v, 0x00030003u, 0x64006400u);
-    h[1] = lop_and_or_s(v, 0x000C000Cu, 0x5C005C00u);
-    h[2] = lop_and_or_s(v, 0x00300030u, 0x54005400u);
-    h[3] = lop_and_or_s(v, 0x00C000C0u, 0x4C004C00u);
-    h[4] = lop_and_or_s(v, 0x03000300u, 0x44004400u);
-    h[5] = lop_and_or_s(v1, 0x00030003u, 0x64006400u);
-    h[6] = lop_and_or_s(v1, 0x000C000Cu, 0x5C005C00u);
-    h[7] = lop_and_or_s(v1, 0x00300030u, 0x54005400u);
-}
-
-__device__ __forceinline__ void mma16816s(float* d, uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
-    asm("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-        : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+// D += A(u8, 16x32) * B(s8, 32x8), int32 accumulate
+__device__ __forceinline__ void imma16832(int* d, uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+    asm("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+        : "+r"(d[0]), "+r"(d[1]), "+r"(d[2]), "+r"(d[3])
         : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
 }
 
@@ -95,10 +79,15 @@ __device__ __forceinline__ uint32_t ldg_nc_u32(const void* p) {
     asm volatile("ld.global.nc.b32 %0, [%1];" : "=r"(v) : "l"(p));
     return v;
 }
+__device__ __forceinline__ uint32_t ldg_nc_u16(const void* p) {
+    uint16_t v;
+    asm volatile("ld.global.nc.b16 %0, [%1];" : "=h"(v) : "l"(p));
+    return v;
+}
 
 // shared memory per warp: its windows of x (extraction order) + the zero block
 __host__ __device__ inline int gemv_s_warp_bytes(int wpw) { return wpw * kWinStride + kZeroBytes; }
-__host__ __device__ inline int gemv_s_smem_bytes(int wpw) { return kSWarps * gemv_s_warp_bytes(wpw) + 2 * kSWarps * 16 * 4; }
+__host__ __device__ inline int gemv_s_smem_bytes(int wpw) { return kSWarps * gemv_s_warp_bytes(wpw) + kRedSlots * kSWarps * 16 * 4; }
 
 __device__ __forceinline__ unsigned long long gtime() {
     unsigned long long v;
@@ -110,8 +99,9 @@ __device__ __forceinline__ unsigned long long gtime() {
 template <bool PDL, bool PROF>
 __global__ void __launch_bounds__(kSThreads, 2) gemv_w2s_kernel(const __half* __restrict__ x, const GemvMats m, int IC,
                                                                 int zw, int total_rb, int wpw,
-                                                                unsigned long long* __restrict__ prof) {
+                                                                unsigned long long* __restrict__ prof, int xrep) {
     extern __shared__ __align__(128) uint8_t smem[];
+    if constexpr (PROF) x += (size_t)(blockIdx.x % xrep) * IC;   // experiment: replicas of x spread the L2 hot spot
     int pslot = 0;
     auto mark = [&]() {
         if constexpr (PROF) {
@@ -131,7 +121,7 @@ __global__ void __launch_bounds__(kSThreads, 2) gemv_w2s_kernel(const __half* __
     const int mywin = warp < nwin ? (nwin - warp + kSWarps - 1) / kSWarps : 0;   // windows warp, warp+8, ...
     uint8_t* wbase = smem + (size_t)warp * gemv_s_warp_bytes(wpw);
     uint8_t* zblock = wbase + (size_t)wpw * kWinStride;
-    float* red = reinterpret_cast<float*>(smem + (size_t)kSWarps * gemv_s_warp_bytes(wpw));   // [2][8][16]
+    float* red = reinterpret_cast<float*>(smem + (size_t)kSWarps * gemv_s_warp_bytes(wpw));   // [kRedSlots][8][16]
 
     // ---- producer cursor: item = (16-channel block, window of this warp)
     int p_rb = rb0, p_j = 0, p_mi = 0;
@@ -150,11 +140,10 @@ __global__ void __launch_bounds__(kSThreads, 2) gemv_w2s_kernel(const __half* __
 #pragma unroll
             for (int i = 0; i < 8; ++i) b.a.r[i] = b.b.r[i] = 0u;
         }
-        const int G0 = 4 * win + 2 * (t & 1);
-        const __half* ps = m.sc[p_mi] + r * zw16 + G0;
-        b.sa = ldg_nc_u32(ps);
-        b.sb = ldg_nc_u32(ps + (size_t)8 * zw16);
-        const uint32_t* pz = m.qz[p_mi] + r * zw + (G0 >> 4);
+        const __half* ps = m.sc[p_mi] + r * zw16 + G;   // G < zw16 always (scales are zero-padded to zw16 columns)
+        b.sa = ldg_nc_u16(ps);
+        b.sb = ldg_nc_u16(ps + (size_t)8 * zw16);
+        const uint32_t* pz = m.qz[p_mi] + r * zw + (G >> 4);
         b.za = ldg_nc_u32(pz);
         b.zb = ldg_nc_u32(pz + (size_t)8 * zw);
         if (++p_j == mywin) {
@@ -190,103 +179,149 @@ __global__ void __launch_bounds__(kSThreads, 2) gemv_w2s_kernel(const __half* __
     mark();   // 1: weight loads issued
     if constexpr (PDL) asm volatile("griddepcontrol.wait;" ::: "memory");
     mark();   // 2: dependency resolved
-    for (int j = 0; j < mywin; ++j) {
-        const int k0 = (warp + kSWarps * j) * 512 + lane * 16;
-        uint32_t in[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-        if (k0 < IC) {
-            const uint4 v0 = ld_coherent_v4(x + k0), v1 = ld_coherent_v4(x + k0 + 8);
-            in[0] = v0.x; in[1] = v0.y; in[2] = v0.z; in[3] = v0.w;
-            in[4] = v1.x; in[5] = v1.y; in[6] = v1.z; in[7] = v1.w;
-        }
-        uint32_t o[8];
-        float bias = 0.f, sum = 0.f;
+    // Each group of 128 activations becomes block fixed point: q = rint(x / unit), |q| <= 8192, unit a power of two
+    // taken from the group's largest magnitude; q = 256 * hi + lo with int8 limbs.  Lane l owns word l of the window
+    // (16 activations); byte j of register i of a limb holds activation i + 4j of the word, the order in which
+    // (word & (0x03030303 << 2i)) presents the codes.
+    for (int j0 = 0; j0 < mywin; j0 += 4) {
+        uint4 raw[4][2];
 #pragma unroll
-        for (int e = 0; e < 8; ++e) {
-            const uint32_t lo = in[e >> 1], hi = in[(e + 8) >> 1];
-            o[e] = (e & 1) ? __byte_perm(lo, hi, 0x7632) : __byte_perm(lo, hi, 0x5410);   // (x[e], x[e+8])
-            const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&o[e]));
-            sum += f.x + f.y;
-            bias = fmaf(ext_ks(e), f.x + f.y, bias);
+        for (int jj = 0; jj < 4; ++jj) {   // all loads of up to 4 windows first: one L2 round trip, not one per window
+            const int k0 = (warp + kSWarps * (j0 + jj)) * 512 + lane * 16;
+            raw[jj][0] = raw[jj][1] = make_uint4(0, 0, 0, 0);
+            if (j0 + jj < mywin && k0 < IC) {
+                raw[jj][0] = ld_coherent_v4(x + k0);
+                raw[jj][1] = ld_coherent_v4(x + k0 + 8);
+            }
         }
-        uint8_t* wj = wbase + (size_t)j * kWinStride;
-        uint4* dst = reinterpret_cast<uint4*>(wj + (lane >> 3) * kGrpStride + (lane & 7) * 32);
-        dst[0] = make_uint4(o[0], o[1], o[2], o[3]);
-        dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
 #pragma unroll
-        for (int s = 1; s < 8; s <<= 1) {
-            bias += __shfl_xor_sync(0xffffffffu, bias, s);
-            sum += __shfl_xor_sync(0xffffffffu, sum, s);
+        for (int jj = 0; jj < 4; ++jj) {
+            if (j0 + jj >= mywin) break;
+            const uint32_t in[8] = {raw[jj][0].x, raw[jj][0].y, raw[jj][0].z, raw[jj][0].w,
+                                    raw[jj][1].x, raw[jj][1].y, raw[jj][1].z, raw[jj][1].w};
+            // largest magnitude of the group (NaN-propagating, so Inf and NaN both end up in the exponent test below)
+            __half2 m2 = __habs2(*reinterpret_cast<const __half2*>(&in[0]));
+#pragma unroll
+            for (int e = 1; e < 8; ++e) m2 = __hmax2_nan(m2, __habs2(*reinterpret_cast<const __half2*>(&in[e])));
+            uint32_t mx = *reinterpret_cast<const uint32_t*>(&m2);
+            mx = max(mx & 0xffffu, mx >> 16);   // |.| bit patterns order like unsigned integers, NaN > Inf > finite
+#pragma unroll
+            for (int sft = 1; sft < 8; sft <<= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, sft));
+            const uint32_t ex = (mx >> 10) & 31u;              // fp16 exponent field: |x| < 2^(max(ex,1) - 14)
+            const uint32_t exc = ex < 1u ? 1u : ex;
+            const float inv_unit = __uint_as_float((154u - exc) << 23);                        // 2^(27 - exc)
+            // unit = 2^(exc - 27): |x / unit| < 8192.  A non-finite activation makes the unit (and the outputs) NaN.
+            const float unit = ex == 31u ? __uint_as_float(0x7fc00000u) : __uint_as_float((exc + 100u) << 23);
+            // q = rint(x / unit) by the 1.5 * 2^23 trick with 128 folded in: bits = 0x4B400080 + q.  With
+            // q = 256 hi + lo, lo in [-128, 127]:  hi = byte 1 of bits, lo = byte 0 of bits ^ 0x80 (both as int8).
+            uint32_t bits[16], qsum = 0;
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                const float2 v = __half22float2(*reinterpret_cast<const __half2*>(&in[e]));
+                bits[2 * e] = __float_as_uint(fmaf(v.x, inv_unit, 12583040.f));
+                bits[2 * e + 1] = __float_as_uint(fmaf(v.y, inv_unit, 12583040.f));
+                qsum += bits[2 * e] + bits[2 * e + 1];
+            }
+            uint32_t hi[4], lo[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {   // byte j of register i <- activation i + 4j
+                const uint32_t p01 = __byte_perm(bits[i], bits[i + 4], 0x5140);        // (lo0, lo1, hi0, hi1)
+                const uint32_t p23 = __byte_perm(bits[i + 8], bits[i + 12], 0x5140);
+                lo[i] = __byte_perm(p01, p23, 0x5410) ^ 0x80808080u;
+                hi[i] = __byte_perm(p01, p23, 0x7632);
+            }
+            uint8_t* wj = wbase + (size_t)(j0 + jj) * kWinStride;
+            const int grp = lane >> 3, w = lane & 7;   // slot = 2*grp + limb; inside: [pair w>>1][w&1][i][j]
+            uint8_t* dst = wj + (2 * grp) * kSlotStride + (w >> 1) * 32 + (w & 1) * 16;
+            *reinterpret_cast<uint4*>(dst) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+            *reinterpret_cast<uint4*>(dst + kSlotStride) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+#pragma unroll
+            for (int sft = 1; sft < 8; sft <<= 1) qsum += __shfl_xor_sync(0xffffffffu, qsum, sft);
+            // 128 elements x 0x4B400080 = 0xA0004000 (mod 2^32)
+            if (w == 0) reinterpret_cast<float2*>(wj + kMetaOff)[grp] = make_float2(unit, (float)(int)(qsum - 0xA0004000u));
         }
-        if ((lane & 7) == 0) reinterpret_cast<float2*>(wj + kMetaOff)[lane >> 3] = make_float2(bias, sum);
     }
     __syncwarp();
     mark();   // 3: x staged
 
     // ---- consumer
-    const bool active = (g == t);
-    const uint8_t* bbase = active ? wbase + t * kGrpStride : zblock + 64;
+    // B column n = 2*group + limb carries x only for the k rows of quad lane t = group: lanes with (g >> 1) == t
+    // read slot g of the window, everyone else reads zeros
+    const bool active = ((g >> 1) == t);
+    const uint8_t* bbase = active ? wbase + g * kSlotStride : zblock;
     const int jstride = active ? kWinStride : 0;
     float fin_lo = 0.f, fin_hi = 0.f;
-    int c_rb = rb0, c_j = 0, c_mi = 0, par = 0;
-    while (c_mi < kMaxMats - 1 && c_rb >= m.rb_end[c_mi]) ++c_mi;
+    int c_j = 0, rslot = 0, rb_base = rb0;
 
+    // Split-K reduction, deferred: every warp parks its partial sums of up to kRedSlots finished 16-channel blocks in
+    // shared memory; one barrier then reduces and stores them all (128 threads, one (block, channel) each).
+    auto block_reduce = [&]() {
+        __syncthreads();
+        if (tid < rslot * 16) {
+            const int sl = tid >> 4, row = tid & 15;
+            const float* rp = red + sl * kSWarps * 16 + row;
+            float acc = 0.f;
+#pragma unroll
+            for (int w = 0; w < kSWarps; ++w) acc += rp[w * 16];
+            const int rb = rb_base + sl;
+            int mi = 0;
+            while (mi < kMaxMats - 1 && rb >= m.rb_end[mi]) ++mi;
+            const int rstart = mi ? m.rb_end[mi - 1] : 0;
+            m.out[mi][(size_t)(rb - rstart) * 16 + row] = __float2half_rn(acc);
+        }
+        rb_base += rslot;
+        rslot = 0;
+        if (rb_base < rb1) __syncthreads();   // the slots are written again
+    };
     auto flush = [&]() {
         fin_lo += __shfl_xor_sync(0xffffffffu, fin_lo, 1);
         fin_hi += __shfl_xor_sync(0xffffffffu, fin_hi, 1);
-        float* my = red + (par * kSWarps + warp) * 16;
+        fin_lo += __shfl_xor_sync(0xffffffffu, fin_lo, 2);
+        fin_hi += __shfl_xor_sync(0xffffffffu, fin_hi, 2);
+        float* my = red + (rslot * kSWarps + warp) * 16;
         if (t == 0) {
             my[g] = fin_lo;
             my[g + 8] = fin_hi;
         }
         fin_lo = fin_hi = 0.f;
-        __syncthreads();
-        if (tid < 16) {
-            const float* rp = red + par * kSWarps * 16 + tid;
-            float acc = 0.f;
-#pragma unroll
-            for (int w = 0; w < kSWarps; ++w) acc += rp[w * 16];
-            const int rstart = c_mi ? m.rb_end[c_mi - 1] : 0;
-            m.out[c_mi][(size_t)(c_rb - rstart) * 16 + tid] = __float2half_rn(acc);
-        }
-        par ^= 1;
-        ++c_rb;
-        while (c_mi < kMaxMats - 1 && c_rb >= m.rb_end[c_mi]) ++c_mi;
+        if (++rslot == kRedSlots) block_reduce();
     };
 
     if (mywin == 0) {   // IC < 4096: this warp owns no window but still takes part in the block reductions
         for (int rb = rb0; rb < rb1; ++rb) flush();
+        if (rslot) block_reduce();
         return;
     }
 
+    // acc[i] collects code digit i of every byte: A = word & (0x03030303 << 2i) is (code << 2i) as uint8, no shifts;
+    // the 4^i factors leave in the float fix-up (all intermediate values are integers below 2^24: exact).
     auto consume = [&](const ItemBuf& b) {
         const uint8_t* bp = bbase + (size_t)c_j * jstride;
-        float d[4][4];
+        int acc[4][4];
 #pragma unroll
-        for (int c = 0; c < 4; ++c) d[c][0] = d[c][1] = d[c][2] = d[c][3] = 0.f;
+        for (int i = 0; i < 4; ++i) acc[i][0] = acc[i][1] = acc[i][2] = acc[i][3] = 0;
 #pragma unroll
-        for (int wd = 0; wd < 8; ++wd) {
-            uint32_t ha[8], hb[8];
-            extract16s(b.a.r[wd], ha);
-            extract16s(b.b.r[wd], hb);
-            const uint4 q0 = *reinterpret_cast<const uint4*>(bp + wd * 32);
-            const uint4 q1 = *reinterpret_cast<const uint4*>(bp + wd * 32 + 16);
-            mma16816s(d[0], ha[0], hb[0], ha[1], hb[1], q0.x, q0.y);
-            mma16816s(d[1], ha[2], hb[2], ha[3], hb[3], q0.z, q0.w);
-            mma16816s(d[2], ha[4], hb[4], ha[5], hb[5], q1.x, q1.y);
-            mma16816s(d[3], ha[6], hb[6], ha[7], hb[7], q1.z, q1.w);
+        for (int p2 = 0; p2 < 4; ++p2) {   // word pair (2 p2, 2 p2 + 1) of the group = 32 codes of each digit
+            const uint4 q0 = *reinterpret_cast<const uint4*>(bp + p2 * 32);        // x limbs for word 2 p2, digits 0..3
+            const uint4 q1 = *reinterpret_cast<const uint4*>(bp + p2 * 32 + 16);   // word 2 p2 + 1
+            const uint32_t a0 = b.a.r[2 * p2], a1 = b.b.r[2 * p2], a2 = b.a.r[2 * p2 + 1], a3 = b.b.r[2 * p2 + 1];
+            imma16832(acc[0], a0 & 0x03030303u, a1 & 0x03030303u, a2 & 0x03030303u, a3 & 0x03030303u, q0.x, q1.x);
+            imma16832(acc[1], a0 & 0x0C0C0C0Cu, a1 & 0x0C0C0C0Cu, a2 & 0x0C0C0C0Cu, a3 & 0x0C0C0C0Cu, q0.y, q1.y);
+            imma16832(acc[2], a0 & 0x30303030u, a1 & 0x30303030u, a2 & 0x30303030u, a3 & 0x30303030u, q0.z, q1.z);
+            imma16832(acc[3], a0 & 0xC0C0C0C0u, a1 & 0xC0C0C0C0u, a2 & 0xC0C0C0C0u, a3 & 0xC0C0C0C0u, q0.w, q1.w);
         }
-        if (t < 2) {   // columns 2t, 2t+1 = groups 2t, 2t+1 of the window
-            const float4 mm = *reinterpret_cast<const float4*>(wbase + (size_t)c_j * kWinStride + kMetaOff + t * 16);
-            const int sh = ((4 * (warp + kSWarps * c_j) + 2 * t) & 15) * 2;
-            const float2 sl = __half22float2(*reinterpret_cast<const __half2*>(&b.sa));
-            const float2 sh2 = __half22float2(*reinterpret_cast<const __half2*>(&b.sb));
-            const float za0 = (float)((b.za >> sh) & 3u), za1 = (float)((b.za >> (sh + 2)) & 3u);
-            const float zb0 = (float)((b.zb >> sh) & 3u), zb1 = (float)((b.zb >> (sh + 2)) & 3u);
-            fin_lo = fmaf(sl.x, ((d[0][0] + d[1][0]) + (d[2][0] + d[3][0])) - fmaf(za0, mm.y, mm.x), fin_lo);
-            fin_lo = fmaf(sl.y, ((d[0][1] + d[1][1]) + (d[2][1] + d[3][1])) - fmaf(za1, mm.w, mm.z), fin_lo);
-            fin_hi = fmaf(sh2.x, ((d[0][2] + d[1][2]) + (d[2][2] + d[3][2])) - fmaf(zb0, mm.y, mm.x), fin_hi);
-            fin_hi = fmaf(sh2.y, ((d[0][3] + d[1][3]) + (d[2][3] + d[3][3])) - fmaf(zb1, mm.w, mm.z), fin_hi);
-        }
+        // this lane's columns 2t, 2t+1 = (hi, lo) limb sums of group t: rows g (acc[.][0..1]) and g+8 (acc[.][2..3])
+        const float2 mt = *reinterpret_cast<const float2*>(wbase + (size_t)c_j * kWinStride + kMetaOff + t * 8);   // (unit, sum q)
+        const int sh = ((4 * (warp + kSWarps * c_j) + t) & 15) * 2;
+        const float za = (float)((b.za >> sh) & 3u), zb = (float)((b.zb >> sh) & 3u);
+        const float sa = __half2float(__ushort_as_half((unsigned short)b.sa)) * mt.x;
+        const float sb = __half2float(__ushort_as_half((unsigned short)b.sb)) * mt.x;
+        float v[4];
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+            v[c] = fmaf((float)acc[3][c], 0.015625f, fmaf((float)acc[2][c], 0.0625f, fmaf((float)acc[1][c], 0.25f, (float)acc[0][c])));
+        fin_lo = fmaf(sa, fmaf(256.f, v[0], v[1]) - za * mt.y, fin_lo);
+        fin_hi = fmaf(sb, fmaf(256.f, v[2], v[3]) - zb * mt.y, fin_hi);
     };
 
     const int nitems = (rb1 - rb0) * mywin;
@@ -300,11 +335,13 @@ __global__ void __launch_bounds__(kSThreads, 2) gemv_w2s_kernel(const __half* __
                 if (++c_j == mywin) {
                     c_j = 0;
                     flush();
-                    mark();   // block reduced + stored
+                    mark();   // block parked (and every kRedSlots blocks: reduced + stored)
                 }
             }
         }
     }
+    if (rslot) block_reduce();
+    mark();
 }
 
 }  // namespace bdq
@@ -384,7 +421,7 @@ int bdq_gemv_w2_stream_launch(const void* x, int nmat, const int32_t* const* qwe
         g_gemv_prof_used += (size_t)grid * kSWarps * 16;
         if (g_gemv_prof_used > g_gemv_prof_cap) return BDQ_ERR_SHAPE;
     }
-    cudaLaunchKernelEx(&cfg, kern, (const __half*)x, m, (int)IC, zw, total_rb, wpw, pbuf);
+    cudaLaunchKernelEx(&cfg, kern, (const __half*)x, m, (int)IC, zw, total_rb, wpw, pbuf, prof ? ((flags >> 8) & 0xff) + 1 : 1);
     return check_launch("bdq_gemv_w2(stream)");
 }
 

@@ -1,0 +1,86 @@
+"""Host-side logic of the multi-GPU path on CPU: partition plans, and the clip-cache / channel-slice all-gathers over a
+world_size-2 gloo group (the same code path NCCL takes on GPUs).  No kernels are called."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from bitdistiller_b200 import sharded as S
+
+
+def test_row_shard_and_layer_owner_cover_everything():
+    for rows, world in [(4096, 8), (11008, 8), (1024, 8), (12288, 8), (4096, 3), (48, 2), (16, 4)]:
+        spans = [S.row_shard(rows, r, world) for r in range(world)]
+        assert spans[0][0] == 0 and spans[-1][1] == rows
+        for (a0, a1), (b0, b1) in zip(spans, spans[1:]):
+            assert a1 == b0 and a0 % 16 == 0 and a1 % 16 == 0
+        sizes = [b - a for a, b in spans]
+        assert max(sizes) - min(sizes) <= 16
+    with pytest.raises(ValueError):
+        S.row_shard(100, 0, 2)
+    for n_layers, world in [(32, 8), (36, 8), (32, 5), (2, 4)]:
+        owners = [S.layer_owner(i, n_layers, world) for i in range(n_layers)]
+        assert owners == sorted(owners)
+        for r in range(world):
+            assert S.owned_layers(n_layers, r, world) == [i for i, o in enumerate(owners) if o == r]
+    with pytest.raises(IndexError):
+        S.layer_owner(32, 32, 8)
+
+
+def test_gather_clip_cache_single_process_is_identity():
+    e = [("a", torch.ones(4, 2, 1), -torch.ones(4, 2, 1))]
+    out = S.gather_clip_cache(e, dtype=torch.float32)
+    assert out[0][0] == "a" and torch.equal(out[0][1], e[0][1]) and torch.equal(out[0][2], e[0][2])
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _clip_of_layer(i):
+    g = torch.Generator().manual_seed(i)
+    out = []
+    for name, co, ng in [("v_proj", 32, 2), ("down_proj", 16, 5 + (i % 2))]:   # ragged sizes across layers
+        mx = torch.rand(co, ng, 1, generator=g).bfloat16()
+        out.append((f"model.layers.{i}.{name}", mx, -mx * 0.5))
+    return out
+
+
+def _worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        n_layers = 5
+        full = S.run_clip_sharded(n_layers, _clip_of_layer, dtype=torch.bfloat16, device=torch.device("cpu"))
+        ref = [e for i in range(n_layers) for e in _clip_of_layer(i)]
+        ok = len(full) == len(ref) and all(a[0] == b[0] and torch.equal(a[1], b[1]) and torch.equal(a[2], b[2])
+                                           for a, b in zip(full, ref))
+        # channel-slice all-gather: decode row and a prefill block
+        for M in (1, 3):
+            whole = torch.arange(M * 64, dtype=torch.float32).view(M, 64).half()
+            r0, r1 = S.row_shard(64, rank, world)
+            got = S.all_gather_cols(whole[:, r0:r1].contiguous())
+            ok = ok and torch.equal(got, whole)
+        q.put((rank, bool(ok)))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_sharded_gathers_world2_gloo():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    ps = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in ps:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in ps)
+    for p in ps:
+        p.join(timeout=60)
+    assert res == [(0, True), (1, True)]

@@ -17,13 +17,17 @@ QWEN3_8B = [("q_proj", 4096, 4096), ("k_proj", 1024, 4096), ("v_proj", 1024, 409
 LAYERS = 36
 
 
-def build(dev, layers=LAYERS, batch=1):
+def build(dev, layers=LAYERS, batch=1, chain=False):
+    """chain=True: a truly dependent decode chain -- every GEMV reads the activation vector the previous launch just
+    wrote (q_proj's output feeds o_proj, o_proj's output feeds gate/up, gate_proj's output feeds down_proj, down_proj's
+    output feeds the next layer's q/k/v; the attention / SiLU math in between is not part of this path), weights scaled
+    so the chain keeps unit variance.  chain=False: every launch has its own static input."""
     proto = {}
     for name, oc, ic in QWEN3_8B:
         if (oc, ic) in proto:
             continue
         g = torch.Generator(device=dev).manual_seed(oc * 7 + ic)
-        w = (torch.randn(oc, ic, device=dev, generator=g) * 0.02).half()
+        w = (torch.randn(oc, ic, device=dev, generator=g) * (ic ** -0.5 if chain else 0.02)).half()
         dq, s, z, _ = Q.int_fakequant(w, 2, 128, 0, want_scale_zp=True)
         proto[(oc, ic)] = pack_wq(dq, s.view(oc, -1), z.view(oc, -1), 2, 128)
     ops = []
@@ -33,6 +37,18 @@ def build(dev, layers=LAYERS, batch=1):
             x = torch.randn(batch, ic, device=dev).half()
             out = torch.empty(batch, oc, device=dev, dtype=torch.float16)
             ops.append((x, qw, qs, qz, out, batch, ic, oc))
+    if chain:
+        assert batch == 1
+        prev_down = None
+        for li in range(layers):
+            o = {n[0]: ops[li * 7 + k] for k, n in enumerate(QWEN3_8B)}
+            src = {"q_proj": prev_down, "k_proj": prev_down, "v_proj": prev_down, "o_proj": o["q_proj"][4],
+                   "gate_proj": o["o_proj"][4], "up_proj": o["o_proj"][4], "down_proj": o["gate_proj"][4]}
+            for k, n in enumerate(QWEN3_8B):
+                if src[n[0]] is not None:
+                    t = ops[li * 7 + k]
+                    ops[li * 7 + k] = (src[n[0]],) + t[1:]
+            prev_down = o["down_proj"][4]
     return ops
 
 
@@ -112,7 +128,9 @@ def graph_time(ops, flags, fused, dev, prefetch=False):
 def main():
     dev = torch.device("cuda:0")
     batch = int(sys.argv[1]) if len(sys.argv) > 1 else 1
-    ops = build(dev, batch=batch)
+    chain = batch == 1 and not (len(sys.argv) > 2 and sys.argv[2] == "static")
+    ops = build(dev, batch=batch, chain=chain)
+    print(f"inputs: {'dependent chain (each launch reads the previous launch output)' if chain else 'static per-launch inputs'}")
     peak = 6548.5
     p = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "MEASURED_PEAKS.json")
     if os.path.exists(p):

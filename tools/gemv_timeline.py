@@ -17,7 +17,10 @@ def main():
     which = sys.argv[1] if len(sys.argv) > 1 else "gate"
     flags = int(sys.argv[2]) if len(sys.argv) > 2 else 1
     pre = len(sys.argv) > 3 and sys.argv[3] == "pf"
-    ops = build(dev, layers=36)
+    xrep = (flags >> 8) & 0xff
+    ops = build(dev, layers=36, chain=(which == "layer"))
+    if xrep:
+        ops = [(o[0].repeat(xrep + 1, 1).contiguous(),) + o[1:] for o in ops]
     fused = False
     if which == "layer":
         sel, fused = ops[: 7 * 12], True
