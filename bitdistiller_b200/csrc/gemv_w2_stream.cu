@@ -32,6 +32,9 @@
 //     scale / zero-point fix-up runs once per group per lane:
 //         out[oc] += s[oc,g] * unit[g] * (256 * HI + LO - z[oc,g] * sum_k q[k])
 //   * non-finite activations make the group's unit NaN, so the affected outputs are NaN (not silently finite).
+#include <cuda.h>
+#include <cstring>
+
 #include "bdq_common.cuh"
 
 namespace bdq {
@@ -54,6 +57,10 @@ struct GemvMats {
     int rb_end[kMaxMats];   // cumulative count of 16-channel blocks
     const uint8_t* pf[kMaxMats];       // L2 prefetch hint: packed weights of the next launch (may be null)
     unsigned long long pf_bytes[kMaxMats];
+};
+
+struct GemvMaps {   // TMA variant: one 2-D tensor map per matrix, [OC rows][IC/4 bytes] uint8, box 16 rows x 128 B, SWIZZLE_128B
+    CUtensorMap m[kMaxMats];
 };
 
 struct ItemBuf {
@@ -85,6 +92,40 @@ __device__ __forceinline__ uint32_t ldg_nc_u16(const void* p) {
     return v;
 }
 
+__device__ __forceinline__ uint32_t gs_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void gs_mbar_init(uint64_t* b, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(gs_smem_u32(b)), "r"(count));
+}
+__device__ __forceinline__ void gs_mbar_expect_tx(uint64_t* b, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(gs_smem_u32(b)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void gs_mbar_wait(uint64_t* b, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "SW_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra SD_%=;\n\t"
+        "bra SW_%=;\n\t"
+        "SD_%=:\n\t}" ::"r"(gs_smem_u32(b)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void gs_tma_load_2d(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
+                     gs_smem_u32(dst)), "l"(map), "r"(c0), "r"(c1), "r"(gs_smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void gs_bulk_load(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(gs_smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(gs_smem_u32(bar)) : "memory");
+}
+
+constexpr int kItemBytes = 2048;   // TMA variant: one item = box of 16 channels x 128 B
+__host__ __device__ inline int gemv_t_meta_bytes(int zw) { return 16 * zw * 32 + 16 * zw * 4; }   // scales + zero words of 16 channels
+// TMA variant layout (from a 1024-aligned base): [8 warps][depth] item slots | per-warp x windows + zero block |
+// [kRedSlots] meta slots | red | barriers
+__host__ __device__ inline int gemv_t_smem_bytes(int wpw, int zw, int depth) {
+    return 1024 + kSWarps * depth * kItemBytes + kSWarps * (wpw * kWinStride + kZeroBytes) + kRedSlots * gemv_t_meta_bytes(zw) +
+           kRedSlots * kSWarps * 16 * 4 + (kSWarps * 8 + kRedSlots) * 8;
+}
+
 // shared memory per warp: its windows of x (extraction order) + the zero block
 __host__ __device__ inline int gemv_s_warp_bytes(int wpw) { return wpw * kWinStride + kZeroBytes; }
 __host__ __device__ inline int gemv_s_smem_bytes(int wpw) { return kSWarps * gemv_s_warp_bytes(wpw) + kRedSlots * kSWarps * 16 * 4; }
@@ -96,11 +137,19 @@ __device__ __forceinline__ unsigned long long gtime() {
 }
 
 // PROF: lane 0 of every warp records %globaltimer at the phase boundaries into prof[cta][warp][16] (dev tool only)
-template <bool PDL, bool PROF>
+template <bool PDL, bool PROF, bool TMA>
 __global__ void __launch_bounds__(kSThreads, 2) gemv_w2s_kernel(const __half* __restrict__ x, const GemvMats m, int IC,
                                                                 int zw, int total_rb, int wpw,
-                                                                unsigned long long* __restrict__ prof, int xrep) {
-    extern __shared__ __align__(128) uint8_t smem[];
+                                                                unsigned long long* __restrict__ prof, int xrep,
+                                                                const __grid_constant__ GemvMaps maps, int depth) {
+    extern __shared__ __align__(128) uint8_t smem_raw[];
+    uint8_t* smem = smem_raw;
+    uint8_t* ring = nullptr;        // TMA: [8 warps][depth][2048]
+    if constexpr (TMA) {
+        smem = smem_raw + ((1024u - (gs_smem_u32(smem_raw) & 1023u)) & 1023u);
+        ring = smem;
+        smem += kSWarps * depth * kItemBytes;
+    }
     if constexpr (PROF) x += (size_t)(blockIdx.x % xrep) * IC;   // experiment: replicas of x spread the L2 hot spot
     int pslot = 0;
     auto mark = [&]() {
@@ -122,6 +171,52 @@ __global__ void __launch_bounds__(kSThreads, 2) gemv_w2s_kernel(const __half* __
     uint8_t* wbase = smem + (size_t)warp * gemv_s_warp_bytes(wpw);
     uint8_t* zblock = wbase + (size_t)wpw * kWinStride;
     float* red = reinterpret_cast<float*>(smem + (size_t)kSWarps * gemv_s_warp_bytes(wpw));   // [kRedSlots][8][16]
+    // TMA variant: meta slots (scales + zero words of one 16-channel block each) and the mbarriers
+    const int meta_bytes = gemv_t_meta_bytes(zw);
+    uint8_t* meta = reinterpret_cast<uint8_t*>(red) + kRedSlots * kSWarps * 16 * 4;
+    uint64_t* wbar = reinterpret_cast<uint64_t*>(meta + kRedSlots * meta_bytes) + warp * 8;   // this warp's item barriers
+    uint64_t* mbar = reinterpret_cast<uint64_t*>(meta + kRedSlots * meta_bytes) + kSWarps * 8;   // [kRedSlots]
+    uint8_t* wring = ring + (size_t)warp * depth * kItemBytes;
+    auto locate = [&](int rb, int& mi, int& r0) {   // 16-channel block -> (matrix, first channel)
+        mi = 0;
+        while (mi < kMaxMats - 1 && rb >= m.rb_end[mi]) ++mi;
+        r0 = (rb - (mi ? m.rb_end[mi - 1] : 0)) * 16;
+    };
+    auto issue_meta = [&](int rb, int slot) {   // one thread: scales + zero words of block rb -> meta slot
+        int mi, r0;
+        locate(rb, mi, r0);
+        uint8_t* dst = meta + slot * meta_bytes;
+        gs_mbar_expect_tx(&mbar[slot], (uint32_t)meta_bytes);
+        gs_bulk_load(dst, m.sc[mi] + (size_t)r0 * zw16, 16 * zw * 32, &mbar[slot]);
+        gs_bulk_load(dst + 16 * zw * 32, m.qz[mi] + (size_t)r0 * zw, 16 * zw * 4, &mbar[slot]);
+    };
+    int t_rb = rb0, t_j = 0, t_slot = 0;   // TMA producer cursor (lane 0 issues)
+    auto issue_tma = [&]() {
+        if (t_rb >= rb1) return;
+        if (lane == 0) {
+            int mi, r0;
+            locate(t_rb, mi, r0);
+            gs_mbar_expect_tx(&wbar[t_slot], kItemBytes);
+            gs_tma_load_2d(wring + t_slot * kItemBytes, &maps.m[mi], (warp + kSWarps * t_j) * 128, r0, &wbar[t_slot]);
+        }
+        if (++t_slot == depth) t_slot = 0;
+        if (++t_j == mywin) {
+            t_j = 0;
+            ++t_rb;
+        }
+    };
+    if constexpr (TMA) {
+        if (lane == 0)
+            for (int d = 0; d < depth; ++d) gs_mbar_init(&wbar[d], 1);
+        if (tid == 0)
+            for (int sl = 0; sl < kRedSlots; ++sl) gs_mbar_init(&mbar[sl], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        __syncthreads();
+        if (tid == 0)
+            for (int sl = 0; sl < kRedSlots && rb0 + sl < rb1; ++sl) issue_meta(rb0 + sl, sl);
+        if (mywin > 0)
+            for (int d = 0; d < depth; ++d) issue_tma();
+    }
 
     // ---- producer cursor: item = (16-channel block, window of this warp)
     int p_rb = rb0, p_j = 0, p_mi = 0;
@@ -152,10 +247,12 @@ __global__ void __launch_bounds__(kSThreads, 2) gemv_w2s_kernel(const __half* __
             while (p_mi < kMaxMats - 1 && p_rb >= m.rb_end[p_mi]) ++p_mi;
         }
     };
-    ItemBuf buf[kDepth];
-    if (mywin > 0) {
+    ItemBuf buf[TMA ? 1 : kDepth];
+    if constexpr (!TMA) {
+        if (mywin > 0) {
 #pragma unroll
-        for (int d = 0; d < kDepth; ++d) issue(buf[d]);   // weights first: nothing here depends on the previous kernel
+            for (int d = 0; d < kDepth; ++d) issue(buf[d]);   // weights first: nothing here depends on the previous kernel
+        }
     }
     // L2 prefetch of the next launch's weights: this CTA's slice, 8 KB per instruction, one lane
     if (tid == 0) {
@@ -271,6 +368,10 @@ __global__ void __launch_bounds__(kSThreads, 2) gemv_w2s_kernel(const __half* __
         }
         rb_base += rslot;
         rslot = 0;
+        if constexpr (TMA) {   // every warp is past the barrier above: the meta slots of the finished blocks are free
+            if (tid == 0)
+                for (int sl = 0; sl < kRedSlots && rb_base + sl < rb1; ++sl) issue_meta(rb_base + sl, sl);
+        }
         if (rb_base < rb1) __syncthreads();   // the slots are written again
     };
     auto flush = [&]() {
@@ -325,6 +426,42 @@ __global__ void __launch_bounds__(kSThreads, 2) gemv_w2s_kernel(const __half* __
     };
 
     const int nitems = (rb1 - rb0) * mywin;
+    if constexpr (TMA) {
+        const uint32_t swz = (uint32_t)(((2 * t) ^ g) * 16);   // SWIZZLE_128B: 16-B chunk c of row r sits at chunk c ^ (r & 7)
+        int c_slot = 0, c_par = 0;
+        for (int i = 0; i < nitems; ++i) {
+            gs_mbar_wait(&wbar[c_slot], (uint32_t)c_par);
+            if (c_j == 0) gs_mbar_wait(&mbar[rslot], (uint32_t)(((rb_base - rb0) / kRedSlots) & 1));
+            const uint8_t* sl = wring + c_slot * kItemBytes;
+            ItemBuf& b = buf[0];
+            {
+                const uint4 a0 = *reinterpret_cast<const uint4*>(sl + g * 128 + swz);
+                const uint4 a1 = *reinterpret_cast<const uint4*>(sl + g * 128 + (swz ^ 16u));
+                const uint4 b0 = *reinterpret_cast<const uint4*>(sl + (g + 8) * 128 + swz);
+                const uint4 b1 = *reinterpret_cast<const uint4*>(sl + (g + 8) * 128 + (swz ^ 16u));
+                b.a.r[0] = a0.x; b.a.r[1] = a0.y; b.a.r[2] = a0.z; b.a.r[3] = a0.w;
+                b.a.r[4] = a1.x; b.a.r[5] = a1.y; b.a.r[6] = a1.z; b.a.r[7] = a1.w;
+                b.b.r[0] = b0.x; b.b.r[1] = b0.y; b.b.r[2] = b0.z; b.b.r[3] = b0.w;
+                b.b.r[4] = b1.x; b.b.r[5] = b1.y; b.b.r[6] = b1.z; b.b.r[7] = b1.w;
+                const uint8_t* ms = meta + rslot * meta_bytes;
+                const int G = 4 * (warp + kSWarps * c_j) + t;
+                b.sa = reinterpret_cast<const unsigned short*>(ms)[g * zw16 + G];
+                b.sb = reinterpret_cast<const unsigned short*>(ms)[(g + 8) * zw16 + G];
+                b.za = reinterpret_cast<const uint32_t*>(ms + 16 * zw * 32)[g * zw + (G >> 4)];
+                b.zb = reinterpret_cast<const uint32_t*>(ms + 16 * zw * 32)[(g + 8) * zw + (G >> 4)];
+            }
+            __syncwarp();   // every lane holds its share of the slot in registers: refill it before the math
+            issue_tma();
+            if (++c_slot == depth) { c_slot = 0; c_par ^= 1; }
+            consume(b);
+            mark();
+            if (++c_j == mywin) {
+                c_j = 0;
+                flush();
+                mark();
+            }
+        }
+    } else {
     for (int i = 0; i < nitems; i += kDepth) {
 #pragma unroll
         for (int d = 0; d < kDepth; ++d) {
@@ -340,6 +477,7 @@ __global__ void __launch_bounds__(kSThreads, 2) gemv_w2s_kernel(const __half* __
             }
         }
     }
+    }
     if (rslot) block_reduce();
     mark();
 }
@@ -347,6 +485,22 @@ __global__ void __launch_bounds__(kSThreads, 2) gemv_w2s_kernel(const __half* __
 }  // namespace bdq
 
 using namespace bdq;
+
+// cuTensorMapEncodeTiled through the runtime's driver entry point lookup (libbdq.so must load on machines without a driver)
+typedef CUresult (*GemvEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                 const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                 CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static GemvEncodeFn gemv_get_encode() {
+    static GemvEncodeFn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = (GemvEncodeFn)p;
+    }
+    return fn;
+}
 
 static unsigned long long* g_gemv_prof = nullptr;
 static size_t g_gemv_prof_cap = 0, g_gemv_prof_used = 0;
@@ -389,14 +543,44 @@ int bdq_gemv_w2_stream_launch(const void* x, int nmat, const int32_t* const* qwe
     if ((uintptr_t)x % 16) return BDQ_ERR_UNSUPPORTED;
     const int nwin = (int)((IC / 128 + 3) / 4);
     const int wpw = (nwin + kSWarps - 1) / kSWarps;
-    const int smem = gemv_s_smem_bytes(wpw);
-    if (smem > 112 * 1024) return BDQ_ERR_UNSUPPORTED;   // two CTAs (this launch + its PDL successor) per SM
     const bool pdl = (flags & BDQ_GEMV_PDL) != 0;
     const bool prof = (flags & BDQ_GEMV_PROF) != 0 && g_gemv_prof != nullptr;
-    auto kern = prof ? (pdl ? gemv_w2s_kernel<true, true> : gemv_w2s_kernel<false, true>)
-                     : (pdl ? gemv_w2s_kernel<true, false> : gemv_w2s_kernel<false, false>);
-    static bool attr_done[4] = {false, false, false, false};
-    const int ai = (prof ? 2 : 0) + (pdl ? 1 : 0);
+    bool tma = (flags & BDQ_GEMV_TMA) != 0;
+    GemvMaps maps;
+    memset(&maps, 0, sizeof(maps));
+    int depth = 0, smem = gemv_s_smem_bytes(wpw);
+    if (tma) {   // item ring depth: as deep as two CTAs per SM allow
+        for (int d = 4; d >= 2 && !depth; --d)
+            if (gemv_t_smem_bytes(wpw, zw, d) <= 112 * 1024) depth = d;
+        for (int i = 0; i < nmat; ++i)
+            if (((uintptr_t)scales[i] % 16) || ((uintptr_t)qzeros[i] % 16)) depth = 0;   // bulk copies need 16-B alignment
+        GemvEncodeFn enc = depth ? gemv_get_encode() : nullptr;
+        if (!enc) {
+            tma = false;   // fall back to the register-streaming variant
+        } else {
+            for (int i = 0; i < kMaxMats; ++i) {
+                const int k = i < nmat ? i : nmat - 1;
+                const cuuint64_t dims[2] = {(cuuint64_t)(IC / 4), (cuuint64_t)OC[k]};   // bytes per row, rows
+                const cuuint64_t strides[1] = {(cuuint64_t)(IC / 4)};
+                const cuuint32_t box[2] = {128, 16};
+                const cuuint32_t estr[2] = {1, 1};
+                CUresult r = enc(&maps.m[i], CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<int32_t*>(qweight[k]), dims, strides,
+                                 box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                 CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                if (r != CUDA_SUCCESS) { set_error("gemv_w2: cuTensorMapEncodeTiled failed (%d)", (int)r); return BDQ_ERR_CUDA; }
+            }
+            smem = gemv_t_smem_bytes(wpw, zw, depth);
+        }
+    }
+    if (smem > 112 * 1024) return BDQ_ERR_UNSUPPORTED;   // two CTAs per SM
+    typedef void (*KernFn)(const __half*, const GemvMats, int, int, int, int, unsigned long long*, int, const GemvMaps, int);
+    static const KernFn kerns[8] = {gemv_w2s_kernel<false, false, false>, gemv_w2s_kernel<true, false, false>,
+                                    gemv_w2s_kernel<false, true, false>,  gemv_w2s_kernel<true, true, false>,
+                                    gemv_w2s_kernel<false, false, true>,  gemv_w2s_kernel<true, false, true>,
+                                    gemv_w2s_kernel<false, true, true>,   gemv_w2s_kernel<true, true, true>};
+    static bool attr_done[8] = {false, false, false, false, false, false, false, false};
+    const int ai = (tma ? 4 : 0) + (prof ? 2 : 0) + (pdl ? 1 : 0);
+    KernFn kern = kerns[ai];
     if (!attr_done[ai]) {
         if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024) != cudaSuccess)
             return check_launch("bdq_gemv_w2(stream attr)");
@@ -421,7 +605,8 @@ int bdq_gemv_w2_stream_launch(const void* x, int nmat, const int32_t* const* qwe
         g_gemv_prof_used += (size_t)grid * kSWarps * 16;
         if (g_gemv_prof_used > g_gemv_prof_cap) return BDQ_ERR_SHAPE;
     }
-    cudaLaunchKernelEx(&cfg, kern, (const __half*)x, m, (int)IC, zw, total_rb, wpw, pbuf, prof ? ((flags >> 8) & 0xff) + 1 : 1);
+    cudaLaunchKernelEx(&cfg, kern, (const __half*)x, m, (int)IC, zw, total_rb, wpw, pbuf, prof ? ((flags >> 8) & 0xff) + 1 : 1,
+                       maps, depth);
     return check_launch("bdq_gemv_w2(stream)");
 }
 

@@ -91,9 +91,11 @@ def test_gemv_w2_vs_oracle(oc, ic, pdl):
 
 
 @pytest.mark.parametrize("oc,ic,flags", [(4096, 4096, 2), (4096, 4096, 4), (4096, 12288, 6), (48, 2176, 0), (48, 2176, 2),
-                                         (16, 128, 1), (1040, 640, 3)])
+                                         (16, 128, 1), (1040, 640, 3), (4096, 4096, 16), (12288, 4096, 17), (4096, 12288, 17),
+                                         (4096, 11008, 16), (48, 2176, 17), (16, 128, 16), (1040, 640, 18)])
 def test_gemv_w2_batch1_variants(oc, ic, flags):
-    """Batch 1 through both kernels: streaming (flags 0/1), one CTA per SM (2), the ring kernel (4); ragged shapes
+    """Batch 1 through both kernels: streaming (flags 0/1), one CTA per SM (2), the ring kernel (4), TMA weight tiles (16);
+    ragged shapes
     (17 groups, 5 groups, a single group)."""
     from bitdistiller_b200 import awq_inference_engine as E
     (qw, qz, qs), dq = _packed_layer(oc, ic, 100 + flags)
@@ -108,16 +110,17 @@ def test_gemv_w2_batch1_variants(oc, ic, flags):
 
 @pytest.mark.parametrize("ocs,ic", [((4096, 1024, 1024), 4096), ((12288, 12288), 4096), ((4096, 48, 16, 1024), 11008)])
 @pytest.mark.parametrize("pdl", [False, True])
-def test_gemv_w2_multi(ocs, ic, pdl):
+@pytest.mark.parametrize("tma", [0, 16])
+def test_gemv_w2_multi(ocs, ic, pdl, tma):
     """Fused q/k/v and gate/up launches: every matrix's output equals its stand-alone GEMV bit for bit (same kernel,
     same summation order) and the oracle within rtol 1e-2."""
     from bitdistiller_b200 import awq_inference_engine as E
     layers = [_packed_layer(oc, ic, 200 + i) for i, oc in enumerate(ocs)]
     x = torch.randn(1, ic, generator=torch.Generator().manual_seed(9)).to(torch.float16).to(dev)
     outs = E.gemv_multi_forward_cuda(x, [l[0][0] for l in layers], [l[0][2] for l in layers], [l[0][1] for l in layers],
-                                     128, pdl=pdl, prefetch=[l[0][0] for l in layers[:2]] if pdl else ())
+                                     128, pdl=pdl, flags=tma, prefetch=[l[0][0] for l in layers[:2]] if pdl else ())
     for ((qw, qz, qs), dq), out in zip(layers, outs):
-        single = E.gemv_forward_cuda(x, qw, qs, qz, 2, 128)
+        single = E.gemv_forward_cuda(x, qw, qs, qz, 2, 128)   # register-streaming variant: same arithmetic, same order
         assert torch.equal(out, single)
         sub = slice(0, min(qw.shape[0], 128))
         ref = oracle.wq_matmul(x.cpu(), qw[sub].cpu(), qz[sub].cpu(), qs[sub].cpu(), 128, 2)

@@ -138,7 +138,7 @@ def main():
     nbytes = bytes_per_token(ops)
     res = {}
     PDL, C1, RING = 1, 2, 4
-    variants = [("ring", RING), ("stream", 0), ("stream 1cta/SM", C1)] if batch == 1 else [("ring", 0)]
+    variants = [("ring", RING), ("stream", 0), ("stream tma", 16)] if batch == 1 else [("ring", 0)]
     for vname, vf in variants:
         for fused in ((False, True) if batch == 1 else (False,)):
             for pname, pf in (("graph", 0), ("graph+pdl", PDL)):
