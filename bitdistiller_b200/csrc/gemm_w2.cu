@@ -15,6 +15,7 @@
 //                 weights are never materialised in fp16 anywhere but in this ring.
 //                 After the k loop the same warps drain TMEM (tcgen05.ld 32x32b) and store fp16 rows of the output.
 #include <cuda.h>
+#include <cstring>
 
 #include "bdq_common.cuh"
 
@@ -106,11 +107,17 @@ __device__ __forceinline__ void gm_dequant16(uint32_t v, __half2 s2, __half2 kz1
     }
 }
 
+struct GemmPeers {   // tensor parallel: this rank's column slice inside the peers' output matrices
+    __half* p[7];
+    int n;
+};
+
 __global__ void __launch_bounds__(kGmThreads, 1) gemm_w2_kernel(const __grid_constant__ CUtensorMap xmap,
                                                                 const uint32_t* __restrict__ qweight,
                                                                 const __half* __restrict__ scales,
                                                                 const uint32_t* __restrict__ qzeros, __half* __restrict__ out,
-                                                                int M, int IC, int OC, int G, int zw) {
+                                                                int M, int IC, int OC, int G, int zw, int ldo,
+                                                                const GemmPeers peers) {
     extern __shared__ uint8_t gm_smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(gm_smem_raw) + 1023) & ~(uintptr_t)1023);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kGmStages * kGmStageBytes);
@@ -252,9 +259,15 @@ __global__ void __launch_bounds__(kGmThreads, 1) gemm_w2_kernel(const __grid_con
                     const __half2 h2 = __floats2half2_rn(__uint_as_float(r[2 * i]), __uint_as_float(r[2 * i + 1]));
                     pk[i] = *reinterpret_cast<const uint32_t*>(&h2);
                 }
-                uint4* dst = reinterpret_cast<uint4*>(out + (size_t)row * OC + n0 + col);
+                const size_t oi = (size_t)row * ldo + n0 + col;   // ldo = row pitch of the output (OC, or the full width under TP)
+                uint4* dst = reinterpret_cast<uint4*>(out + oi);
 #pragma unroll
                 for (int i = 0; i < 4; ++i) dst[i] = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+                for (int pr = 0; pr < peers.n; ++pr) {   // tensor parallel: the same tile into every peer's output (NVLink stores)
+                    uint4* pd = reinterpret_cast<uint4*>(peers.p[pr] + oi);
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) pd[i] = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+                }
             }
         }
     }
@@ -280,7 +293,11 @@ static EncodeTiledFn get_encode_tiled() {
 }
 
 int launch_gemm_w2(const void* x, const int32_t* qweight, const void* scales, const int32_t* qzeros, void* out, int64_t M,
-                   int64_t IC, int64_t OC, int group, int zw, cudaStream_t st) {
+                   int64_t IC, int64_t OC, int group, int zw, cudaStream_t st, int64_t ldo, int n_peer, void* const* peer_out) {
+    GemmPeers peers;
+    memset(&peers, 0, sizeof(peers));
+    peers.n = n_peer;
+    for (int i = 0; i < n_peer; ++i) peers.p[i] = (__half*)peer_out[i];
     EncodeTiledFn enc = get_encode_tiled();
     if (!enc) { set_error("gemm_w2: cuTensorMapEncodeTiled is not available from this driver"); return BDQ_ERR_CUDA; }
     CUtensorMap map;
@@ -300,7 +317,7 @@ int launch_gemm_w2(const void* x, const int32_t* qweight, const void* scales, co
     }
     dim3 grid((unsigned)(OC / kGmN), (unsigned)((M + kGmM - 1) / kGmM));
     gemm_w2_kernel<<<grid, kGmThreads, kGmSmem, st>>>(map, (const uint32_t*)qweight, (const __half*)scales, (const uint32_t*)qzeros,
-                                                      (__half*)out, (int)M, (int)IC, (int)OC, group, zw);
+                                                      (__half*)out, (int)M, (int)IC, (int)OC, group, zw, (int)ldo, peers);
     return check_launch("bdq_gemm_w2");
 }
 
@@ -323,7 +340,28 @@ extern "C" int bdq_gemm_w2(const void* x, const int32_t* qweight, const void* sc
     if (!x || !qweight || !scales || !qzeros || !out) { set_error("null tensor pointer"); return BDQ_ERR_SHAPE; }
     const bool fast = (group == 128 || group == 64) && IC % 128 == 0 && OC % kGmN == 0 && ((uintptr_t)x % 16 == 0) &&
                       ((uintptr_t)qweight % 32 == 0) && ((uintptr_t)out % 16 == 0) && M < (1ll << 31) && IC < (1 << 24);
-    if (fast) return launch_gemm_w2(x, qweight, scales, qzeros, out, M, IC, OC, group, zw, (cudaStream_t)stream);
+    if (fast) return launch_gemm_w2(x, qweight, scales, qzeros, out, M, IC, OC, group, zw, (cudaStream_t)stream, OC, 0, nullptr);
     // shapes the tcgen05 tile does not cover: stream the weights once per 8 rows through the GEMV kernel (correct, slow)
     return bdq_gemv_w2(x, qweight, scales, qzeros, out, M, IC, OC, group, 0, stream);
+}
+
+// Tensor-parallel prefill GEMM with the all-gather fused into the epilogue: this rank's [M, OC_local] tile block is
+// written at row pitch `ldo` (the full output width) into its own output and, over NVLink peer memory, into every
+// peer's output at the same position.  out / peer_out[p] already point at this rank's first column.  tcgen05 shapes only.
+extern "C" int bdq_gemm_w2_tp(const void* x, const int32_t* qweight, const void* scales, const int32_t* qzeros, void* out,
+                              int64_t M, int64_t IC, int64_t OC_local, int group, int64_t ldo, int n_peer, void* const* peer_out,
+                              bdq_stream_t stream) {
+    if (M <= 0 || IC <= 0 || OC_local <= 0 || ldo < OC_local || n_peer < 0 || n_peer > 7 || (n_peer > 0 && !peer_out) || !x ||
+        !qweight || !scales || !qzeros || !out) {
+        set_error("gemm_w2_tp: bad arguments (M=%lld IC=%lld OC_local=%lld ldo=%lld n_peer=%d)", (long long)M, (long long)IC,
+                  (long long)OC_local, (long long)ldo, n_peer);
+        return BDQ_ERR_SHAPE;
+    }
+    const int zw = bdq_zeros_width(IC, group, 2);
+    const bool fast = zw >= 0 && (group == 128 || group == 64) && IC % 128 == 0 && OC_local % kGmN == 0 && ((uintptr_t)x % 16 == 0) &&
+                      ((uintptr_t)qweight % 32 == 0) && ((uintptr_t)out % 16 == 0) && ldo % 8 == 0 && M < (1ll << 31) && IC < (1 << 24);
+    if (!fast) { set_error("gemm_w2_tp: needs group 64/128, IC %% 128 == 0, OC_local %% %d == 0", kGmN); return BDQ_ERR_UNSUPPORTED; }
+    for (int i = 0; i < n_peer; ++i)
+        if (!peer_out[i] || ((uintptr_t)peer_out[i] % 16)) { set_error("gemm_w2_tp: peer pointer %d null or misaligned", i); return BDQ_ERR_ALIGN; }
+    return launch_gemm_w2(x, qweight, scales, qzeros, out, M, IC, OC_local, group, zw, (cudaStream_t)stream, ldo, n_peer, peer_out);
 }

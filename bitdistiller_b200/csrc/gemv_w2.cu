@@ -334,7 +334,8 @@ using namespace bdq;
 
 int bdq_gemv_w2_stream_launch(const void* x, int nmat, const int32_t* const* qweight, const void* const* scales,
                               const int32_t* const* qzeros, void* const* out, const int64_t* OC, int64_t IC, int flags,
-                              cudaStream_t st, int n_prefetch, const void* const* prefetch, const int64_t* prefetch_bytes);
+                              cudaStream_t st, int n_prefetch, const void* const* prefetch, const int64_t* prefetch_bytes,
+                              int n_peer, void* const* peer_out);
 
 extern "C" int bdq_gemv_w2(const void* x, const int32_t* qweight, const void* scales, const int32_t* qzeros, void* out,
                            int64_t B, int64_t IC, int64_t OC, int group, int flags, bdq_stream_t stream) {
@@ -355,7 +356,7 @@ extern "C" int bdq_gemv_w2(const void* x, const int32_t* qweight, const void* sc
         const int32_t* qz1[1] = {qzeros};
         void* out1[1] = {out};
         const int64_t oc1[1] = {OC};
-        const int rc = bdq_gemv_w2_stream_launch(x, 1, qw1, sc1, qz1, out1, oc1, IC, flags, st, 0, nullptr, nullptr);
+        const int rc = bdq_gemv_w2_stream_launch(x, 1, qw1, sc1, qz1, out1, oc1, IC, flags, st, 0, nullptr, nullptr, 0, nullptr);
         if (rc != BDQ_ERR_UNSUPPORTED) return rc;
     }
     const bool fast = group == 128 && OC % 16 == 0 && ((uintptr_t)x % 16 == 0) && ((uintptr_t)qweight % 16 == 0) &&

@@ -47,6 +47,7 @@ constexpr int kMetaOff = 8 * kSlotStride;   // (unit, sum of quantised x) per gr
 constexpr int kWinStride = 1280;       // 8 slots + meta, padded to a multiple of 128
 constexpr int kZeroBytes = 256;        // per-warp zero block read by the lanes whose B column is empty
 constexpr int kMaxMats = 4;
+constexpr int kMaxPeers = 7;            // other GPUs of an 8-GPU NVLink box
 constexpr int kRedSlots = 8;           // finished 16-channel blocks parked per CTA between split-K reductions
 
 struct GemvMats {
@@ -57,6 +58,8 @@ struct GemvMats {
     int rb_end[kMaxMats];   // cumulative count of 16-channel blocks
     const uint8_t* pf[kMaxMats];       // L2 prefetch hint: packed weights of the next launch (may be null)
     unsigned long long pf_bytes[kMaxMats];
+    __half* peer[kMaxMats][kMaxPeers];  // tensor parallel: the same channel slice inside every peer GPU's output row
+    int npeer;
 };
 
 struct GemvMaps {   // TMA variant: one 2-D tensor map per matrix, [OC rows][IC/4 bytes] uint8, box 16 rows x 128 B, SWIZZLE_128B
@@ -364,7 +367,10 @@ __global__ void __launch_bounds__(kSThreads, 2) gemv_w2s_kernel(const __half* __
             int mi = 0;
             while (mi < kMaxMats - 1 && rb >= m.rb_end[mi]) ++mi;
             const int rstart = mi ? m.rb_end[mi - 1] : 0;
-            m.out[mi][(size_t)(rb - rstart) * 16 + row] = __float2half_rn(acc);
+            const __half hv = __float2half_rn(acc);
+            const size_t oi = (size_t)(rb - rstart) * 16 + row;
+            m.out[mi][oi] = hv;
+            for (int pr = 0; pr < m.npeer; ++pr) m.peer[mi][pr][oi] = hv;   // NVLink peer stores (all-gather fused in the epilogue)
         }
         rb_base += rslot;
         rslot = 0;
@@ -516,11 +522,20 @@ extern "C" int bdq_gemv_set_prof(void* buf, int64_t cap) {
 // streaming kernel so the caller can take the ring kernel instead.
 int bdq_gemv_w2_stream_launch(const void* x, int nmat, const int32_t* const* qweight, const void* const* scales,
                               const int32_t* const* qzeros, void* const* out, const int64_t* OC, int64_t IC, int flags,
-                              cudaStream_t st, int n_prefetch, const void* const* prefetch, const int64_t* prefetch_bytes) {
+                              cudaStream_t st, int n_prefetch, const void* const* prefetch, const int64_t* prefetch_bytes,
+                              int n_peer, void* const* peer_out) {
     if (nmat < 1 || nmat > kMaxMats || IC <= 0 || IC % 128 != 0 || IC > (1 << 20)) return BDQ_ERR_UNSUPPORTED;
     const int zw = bdq_zeros_width(IC, 128, 2);
     if (zw < 0) return BDQ_ERR_UNSUPPORTED;
     GemvMats m;
+    memset(&m, 0, sizeof(m));
+    if (n_peer < 0 || n_peer > kMaxPeers || (n_peer > 0 && !peer_out)) return BDQ_ERR_UNSUPPORTED;
+    m.npeer = n_peer;
+    for (int i = 0; i < nmat && i < kMaxMats; ++i)
+        for (int pr = 0; pr < n_peer; ++pr) {
+            if (!peer_out[i * n_peer + pr]) return BDQ_ERR_UNSUPPORTED;
+            m.peer[i][pr] = (__half*)peer_out[i * n_peer + pr];
+        }
     int total_rb = 0;
     for (int i = 0; i < kMaxMats; ++i) {
         const int k = i < nmat ? i : nmat - 1;
@@ -629,7 +644,7 @@ extern "C" int bdq_gemv_w2_multi(const void* x, int nmat, const int32_t* const* 
         }
     int rc = (group == 128 && !(flags & BDQ_GEMV_RING))
                  ? bdq_gemv_w2_stream_launch(x, nmat, qweight, scales, qzeros, out, OC, IC, flags, (cudaStream_t)stream,
-                                             n_prefetch, prefetch, prefetch_bytes)
+                                             n_prefetch, prefetch, prefetch_bytes, 0, nullptr)
                  : BDQ_ERR_UNSUPPORTED;
     if (rc != BDQ_ERR_UNSUPPORTED) return rc;
     for (int i = 0; i < nmat; ++i) {   // shapes the fused kernel does not take: one launch per matrix
@@ -637,4 +652,24 @@ extern "C" int bdq_gemv_w2_multi(const void* x, int nmat, const int32_t* const* 
         if (rc) return rc;
     }
     return BDQ_OK;
+}
+
+// Tensor-parallel decode GEMV with the all-gather fused into the epilogue: every rank computes its channel slice and
+// writes it into its own output row AND, over NVLink peer memory, into the same slice of every peer's output row
+// (the reference has no tensor parallelism).  out[i] = this rank's slice inside its own full row,
+// peer_out[i * n_peer + p] = the same slice inside peer p's row (peer-mapped device pointers, e.g. from symmetric
+// memory).  The caller orders the consumers behind a cross-rank barrier.
+extern "C" int bdq_gemv_w2_tp(const void* x, int nmat, const int32_t* const* qweight, const void* const* scales,
+                              const int32_t* const* qzeros, void* const* out, const int64_t* OC_local, int64_t IC, int group,
+                              int flags, int n_peer, void* const* peer_out, bdq_stream_t stream) {
+    if (nmat < 1 || nmat > kMaxMats || !x || !qweight || !scales || !qzeros || !out || !OC_local || n_peer < 0 ||
+        n_peer > kMaxPeers || (n_peer > 0 && !peer_out)) {
+        set_error("gemv_w2_tp: 1..%d matrices, 0..%d peers and non-null argument arrays required", kMaxMats, kMaxPeers);
+        return BDQ_ERR_SHAPE;
+    }
+    if (group != 128) { set_error("gemv_w2_tp: group must be 128"); return BDQ_ERR_UNSUPPORTED; }
+    const int rc = bdq_gemv_w2_stream_launch(x, nmat, qweight, scales, qzeros, out, OC_local, IC, flags, (cudaStream_t)stream, 0,
+                                             nullptr, nullptr, n_peer, peer_out);
+    if (rc == BDQ_ERR_UNSUPPORTED) set_error("gemv_w2_tp: shape / alignment not supported by the batch-1 kernel");
+    return rc;
 }

@@ -153,3 +153,72 @@ class TPWQLinear(nn.Module):
             y = y + self.bias
         y = all_gather_cols(y, self.group)
         return y.reshape(x.shape[:-1] + (self.out_features,))
+
+
+# ------------------------------------------------------------------------------------------------- fused all-gather
+class SymmRows:
+    """[M, OC] fp16 output rows allocated in torch symmetric memory: the same buffer exists on every rank of the group
+    and every rank holds peer-mapped pointers to all of them (NVLink).  The tensor-parallel GEMV / GEMM epilogues store
+    their channel slice straight into all of these buffers (bdq_gemv_w2_tp / bdq_gemm_w2_tp), so no collective runs --
+    only `barrier()` between the producers and the consumers of the gathered rows."""
+
+    def __init__(self, M, OC, device, group=None):
+        import torch.distributed._symmetric_memory as symm_mem
+        self.group = group if group is not None else dist.group.WORLD
+        self.t = symm_mem.empty((M, OC), dtype=torch.float16, device=device)
+        self.hdl = symm_mem.rendezvous(self.t, self.group)
+        self.rank, self.world = self.hdl.rank, self.hdl.world_size
+        self.M, self.OC = M, OC
+        self.ptrs = [int(p) for p in self.hdl.buffer_ptrs]
+
+    def slice_ptrs(self, col0):
+        """(own pointer, [peer pointers]) of column col0 of row 0."""
+        off = col0 * 2
+        return self.ptrs[self.rank] + off, [self.ptrs[p] + off for p in range(self.world) if p != self.rank]
+
+    def barrier(self):
+        self.hdl.barrier(channel=0)
+
+
+def tp_gemv_fused(x, shards, rows, flags=0):
+    """Decode: up to 4 column-parallel shards [(qweight, scales, qzeros)] sharing x [1, IC] in ONE launch whose epilogue
+    writes every slice into all ranks' `rows[i]` (SymmRows [1, OC_i]).  Call rows[0].barrier() before reading them."""
+    import ctypes
+
+    from . import _lib as L
+    n = len(shards)
+    ic = x.shape[-1]
+    qw = (ctypes.c_void_p * n)(*[s[0].data_ptr() for s in shards])
+    sc = (ctypes.c_void_p * n)(*[s[1].data_ptr() for s in shards])
+    qz = (ctypes.c_void_p * n)(*[s[2].data_ptr() for s in shards])
+    ocl = (ctypes.c_int64 * n)(*[s[0].shape[0] for s in shards])
+    own, peers = [], []
+    for s, r in zip(shards, rows):
+        o, p = r.slice_ptrs(r.rank * s[0].shape[0])
+        own.append(o)
+        peers += p
+    npeer = rows[0].world - 1
+    outp = (ctypes.c_void_p * n)(*own)
+    peerp = (ctypes.c_void_p * max(len(peers), 1))(*peers)
+    with torch.cuda.device(x.device):
+        rc = L.lib().bdq_gemv_w2_tp(L.ptr(x), n, qw, sc, qz, outp, ocl, L.i64(ic), 128, int(flags), npeer, peerp,
+                                    L.stream_ptr(x.device))
+    L.check(rc, "bdq_gemv_w2_tp")
+
+
+def tp_gemm_fused(x, shard, rows, group_size=128):
+    """Prefill: x [M, IC] times one column-parallel shard; the tcgen05 epilogue writes the [M, OC/n] block at the
+    full-width row pitch into all ranks' `rows` (SymmRows [>=M, OC])."""
+    import ctypes
+
+    from . import _lib as L
+    qweight, scales, qzeros = shard
+    M, ic = x.shape
+    ocl = qweight.shape[0]
+    own, peers = rows.slice_ptrs(rows.rank * ocl)
+    peerp = (ctypes.c_void_p * max(len(peers), 1))(*peers)
+    with torch.cuda.device(x.device):
+        rc = L.lib().bdq_gemm_w2_tp(L.ptr(x), L.ptr(qweight), L.ptr(scales), L.ptr(qzeros), ctypes.c_void_p(own), L.i64(M),
+                                    L.i64(ic), L.i64(ocl), int(group_size), L.i64(rows.OC), len(peers), peerp,
+                                    L.stream_ptr(x.device))
+    L.check(rc, "bdq_gemm_w2_tp")

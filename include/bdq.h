@@ -154,6 +154,23 @@ int bdq_gemm_w2(const void* x, const int32_t* qweight, const void* scales, const
                 int64_t IC, int64_t OC, int group, bdq_stream_t stream);
 
 /*
+ * Tensor-parallel variants with the all-gather of the channel slices FUSED into the kernel epilogue (the
+ * reference has no tensor parallelism: these are the column-parallel shards of WQLinear, qmodule.py:62-66).  Every rank
+ * holds rows [r*OC/n, (r+1)*OC/n) of qweight / scales / qzeros, computes its slice and stores it into its own output
+ * AND, with plain stores over NVLink peer memory, into the same position of every peer's output.  `out` and
+ * `peer_out[...]` already point at this rank's first output channel inside the full-width rows; the peer pointers are
+ * peer-mapped device addresses (e.g. torch symmetric memory `buffer_ptrs`).  The caller puts a cross-rank barrier between
+ * these launches and the consumers of the gathered rows.
+ *   bdq_gemv_w2_tp: batch-1 decode, up to 4 matrices sharing x (peer_out is [nmat][n_peer], row-major), group 128.
+ *   bdq_gemm_w2_tp: prefill, output row pitch `ldo` elements (the full OC), tcgen05 shapes only (OC_local % 256 == 0).
+ */
+int bdq_gemv_w2_tp(const void* x, int nmat, const int32_t* const* qweight, const void* const* scales,
+                   const int32_t* const* qzeros, void* const* out, const int64_t* OC_local, int64_t IC, int group, int flags,
+                   int n_peer, void* const* peer_out, bdq_stream_t stream);
+int bdq_gemm_w2_tp(const void* x, const int32_t* qweight, const void* scales, const int32_t* qzeros, void* out, int64_t M,
+                   int64_t IC, int64_t OC_local, int group, int64_t ldo, int n_peer, void* const* peer_out, bdq_stream_t stream);
+
+/*
  * Two-sided clip-ratio grid search = auto_2clip_layer (quantization/autoclip.py:13-83), all candidates of all
  * (output channel, group) pairs in one launch.  w [co, ci] (T, row-major); x = the calibration activations
  * [n_tok, ci] of the same dtype with a row stride of x_row_stride elements (the reference's token sub-sampling

@@ -187,3 +187,39 @@ def test_wqlinear_forward_decode_matches_dequant():
     assert set(sd) == {"qweight", "qzeros", "scales", "bias"}
     with pytest.raises(NotImplementedError):
         WQLinear(3, 128, 128, 128, False, dev)
+
+
+def test_tp_epilogues_write_own_and_peer_slices():
+    """bdq_gemv_w2_tp / bdq_gemm_w2_tp on one GPU with a second local buffer standing in for the peer: both buffers
+    receive the rank's channel slice at the right column offset and equal the plain kernels' outputs bit for bit."""
+    import ctypes
+    from bitdistiller_b200 import _lib as L
+    from bitdistiller_b200 import awq_inference_engine as E
+    from bitdistiller_b200.triton_kernels import gemm_w2
+    lib = L.lib()
+    (qw, qz, qs), _ = _packed_layer(1024, 4096, 55)
+    half = 512                                   # "rank 1 of 2": channels [512, 1024)
+    sq, sz, ss = qw[half:].contiguous(), qz[half:].contiguous(), qs[half:].contiguous()
+    st = L.stream_ptr(dev)
+    # decode
+    x = torch.randn(1, 4096, generator=torch.Generator().manual_seed(2)).half().to(dev)
+    ref = E.gemv_forward_cuda(x, qw, qs, qz, 2, 128)
+    mine = torch.zeros(1, 1024, dtype=torch.float16, device=dev)
+    peer = torch.zeros(1, 1024, dtype=torch.float16, device=dev)
+    arr = lambda *ps: (ctypes.c_void_p * len(ps))(*ps)
+    rc = lib.bdq_gemv_w2_tp(L.ptr(x), 1, arr(sq.data_ptr()), arr(ss.data_ptr()), arr(sz.data_ptr()),
+                            arr(mine.data_ptr() + half * 2), (ctypes.c_int64 * 1)(512), L.i64(4096), 128, 0, 1,
+                            arr(peer.data_ptr() + half * 2), st)
+    L.check(rc, "bdq_gemv_w2_tp")
+    assert torch.equal(mine[:, half:], ref[:, half:]) and torch.equal(peer[:, half:], ref[:, half:])
+    assert not mine[:, :half].any() and not peer[:, :half].any()
+    # prefill
+    xm = torch.randn(192, 4096, generator=torch.Generator().manual_seed(3)).half().to(dev)
+    refm = gemm_w2(xm, qw, qs, qz, 128)
+    mine = torch.zeros(192, 1024, dtype=torch.float16, device=dev)
+    peer = torch.zeros(192, 1024, dtype=torch.float16, device=dev)
+    rc = lib.bdq_gemm_w2_tp(L.ptr(xm), L.ptr(sq), L.ptr(ss), L.ptr(sz), ctypes.c_void_p(mine.data_ptr() + half * 2),
+                            L.i64(192), L.i64(4096), L.i64(512), 128, L.i64(1024), 1, arr(peer.data_ptr() + half * 2), st)
+    L.check(rc, "bdq_gemm_w2_tp")
+    assert torch.equal(mine[:, half:], refm[:, half:]) and torch.equal(peer[:, half:], refm[:, half:])
+    assert not mine[:, :half].any() and not peer[:, :half].any()

@@ -142,7 +142,99 @@ def bench_tp(dev, rank, world, layers=36):
         else:
             flop = 2.0 * M * sum(oc * ic for _, oc, ic in QWEN3_8B) * layers
             res[label] = {"ms": t * 1e3, "tflops_aggregate": flop / t / 1e12}
+    if world > 1:
+        try:
+            res["fused_epilogue"] = bench_tp_fused(dev, rank, world, shards, ops, layers)
+        except Exception as e:  # symmetric memory needs P2P-capable GPUs; report instead of failing the whole run
+            res["fused_epilogue"] = {"unavailable": f"{type(e).__name__}: {e}"[:300]}
     return res
+
+
+def bench_tp_fused(dev, rank, world, shards, ops, layers):
+    """Same workloads with the all-gather fused into the GEMV / GEMM epilogues (NVLink peer stores into symmetric
+    memory, one cross-rank barrier per launch instead of an NCCL all-gather per linear)."""
+    from bitdistiller_b200.awq_inference_engine import gemv_forward_cuda
+    from bitdistiller_b200.triton_kernels import gemm_w2
+    out = {}
+    M = 2048
+    rows1 = {oc: S.SymmRows(1, oc, dev) for oc in (4096, 1024, 12288)}
+    rowsM = {oc: S.SymmRows(M, oc, dev) for oc in (4096, 1024, 12288)}
+    # parity against the NCCL-gathered result (bit-equal to the single-GPU result, checked above)
+    ok = True
+    for (oc, ic), (sq, sz, ss) in shards.items():
+        x = torch.randn(1, ic, device=dev, generator=torch.Generator(device=dev).manual_seed(7)).half()
+        ref = S.all_gather_cols(gemv_forward_cuda(x, sq, ss, sz, 2, 128))
+        S.tp_gemv_fused(x, [(sq, ss, sz)], [rows1[oc]])
+        rows1[oc].barrier()
+        ok = ok and torch.equal(rows1[oc].t, ref)
+        xm = torch.randn(256, ic, device=dev, generator=torch.Generator(device=dev).manual_seed(8)).half()
+        if sq.shape[0] % 256 == 0:
+            refm = S.all_gather_cols(gemm_w2(xm, sq, ss, sz, 128))
+            S.tp_gemm_fused(xm, (sq, ss, sz), rowsM[oc])
+            rowsM[oc].barrier()
+            ok = ok and torch.equal(rowsM[oc].t[:256], refm)
+        rows1[oc].barrier()
+    out["fused_equals_nccl_gather"] = bool(ok)
+    names = [n for n, _, _ in QWEN3_8B]
+    x1 = {ic: torch.randn(1, ic, device=dev).half() for ic in (4096, 12288)}
+
+    def token_decode():
+        for li in range(layers):
+            o = {n: ops[li * 7 + k] for k, n in enumerate(names)}
+            for grp in (("q_proj", "k_proj", "v_proj"), ("o_proj",), ("gate_proj", "up_proj"), ("down_proj",)):
+                sh = [(o[n][0], o[n][2], o[n][1]) for n in grp]
+                # q / gate own the full-size rows; k, v and up get their own so the slices do not collide
+                rws = [rows1[o[n][3]] if i == 0 else extra[(n, o[n][3])] for i, n in enumerate(grp)]
+                S.tp_gemv_fused(x1[o[grp[0]][4]], sh, rws, flags=1)
+                rws[0].barrier()
+    extra = {("k_proj", 1024): rows1[1024], ("v_proj", 1024): S.SymmRows(1, 1024, dev), ("up_proj", 12288): S.SymmRows(1, 12288, dev)}
+    token_decode()
+    torch.cuda.synchronize()
+    dist.barrier()
+    mode = "eager"
+    run = token_decode
+    try:
+        st = torch.cuda.Stream(dev)
+        with torch.cuda.stream(st):
+            gr = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gr, stream=st):
+                token_decode()
+        gr.replay()
+        torch.cuda.synchronize()
+        run, mode = gr.replay, "CUDA graph"
+    except Exception as e:
+        out["graph_capture_failed"] = f"{type(e).__name__}: {e}"[:200]
+        torch.cuda.synchronize()
+    dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(10):
+        run()
+    e1.record()
+    torch.cuda.synchronize()
+    t = max_over_ranks(e0.elapsed_time(e1) * 1e-3 / 10, dev)
+    out["decode_b1"] = {"us_per_token": t * 1e6, "tok_s": 1 / t, "launch_mode": mode + ", 4 fused launches + 4 symmetric-memory barriers per layer"}
+    xm = {ic: torch.randn(M, ic, device=dev).half() for ic in (4096, 12288)}
+
+    def prefill():
+        for sq, sz, ss, oc, ic in ops:
+            if sq.shape[0] % 256 == 0:
+                S.tp_gemm_fused(xm[ic], (sq, ss, sz), rowsM[oc])
+                rowsM[oc].barrier()
+            else:
+                S.all_gather_cols(gemm_w2(xm[ic], sq, ss, sz, 128))
+    prefill()
+    torch.cuda.synchronize()
+    dist.barrier()
+    e0.record()
+    for _ in range(3):
+        prefill()
+    e1.record()
+    torch.cuda.synchronize()
+    t = max_over_ranks(e0.elapsed_time(e1) * 1e-3 / 3, dev)
+    flop = 2.0 * M * sum(oc * ic for _, oc, ic in QWEN3_8B) * layers
+    out["prefill_m2048"] = {"ms": t * 1e3, "tflops_aggregate": flop / t / 1e12}
+    return out
 
 
 def main():
