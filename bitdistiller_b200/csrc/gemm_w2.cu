@@ -181,7 +181,7 @@ __global__ void __launch_bounds__(kGmThreads, 1) gemm_w2_kernel(const __grid_con
     } else {
         // ================= dequant producers: thread j <-> output channel n0 + j =================
         const int j = tid - 64;
-        const int oc = n0 + j;
+        const int oc = min(n0 + j, OC - 1);   // a partial last tile re-reads the last channel; its columns are never stored
         const int wpr = IC >> 4;
         const uint32_t* wrow = qweight + (size_t)oc * wpr;
         const __half* srow = scales + (size_t)oc * zw * 16;
@@ -252,7 +252,7 @@ __global__ void __launch_bounds__(kGmThreads, 1) gemm_w2_kernel(const __grid_con
                   "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
                 : "r"(taddr));
             asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-            if (row < M) {
+            if (row < M && n0 + col + 32 <= OC) {
                 uint32_t pk[16];
 #pragma unroll
                 for (int i = 0; i < 16; ++i) {
@@ -315,7 +315,7 @@ int launch_gemm_w2(const void* x, const int32_t* qweight, const void* scales, co
             return check_launch("bdq_gemm_w2(attr)");
         attr_done = true;
     }
-    dim3 grid((unsigned)(OC / kGmN), (unsigned)((M + kGmM - 1) / kGmM));
+    dim3 grid((unsigned)((OC + kGmN - 1) / kGmN), (unsigned)((M + kGmM - 1) / kGmM));
     gemm_w2_kernel<<<grid, kGmThreads, kGmSmem, st>>>(map, (const uint32_t*)qweight, (const __half*)scales, (const uint32_t*)qzeros,
                                                       (__half*)out, (int)M, (int)IC, (int)OC, group, zw, (int)ldo, peers);
     return check_launch("bdq_gemm_w2");
@@ -338,7 +338,7 @@ extern "C" int bdq_gemm_w2(const void* x, const int32_t* qweight, const void* sc
     if (zw < 0) { set_error("gemm_w2: group=%d unsupported", group); return BDQ_ERR_UNSUPPORTED; }
     if (M == 0) return BDQ_OK;
     if (!x || !qweight || !scales || !qzeros || !out) { set_error("null tensor pointer"); return BDQ_ERR_SHAPE; }
-    const bool fast = (group == 128 || group == 64) && IC % 128 == 0 && OC % kGmN == 0 && ((uintptr_t)x % 16 == 0) &&
+    const bool fast = (group == 128 || group == 64) && IC % 128 == 0 && OC % 32 == 0 && ((uintptr_t)x % 16 == 0) &&
                       ((uintptr_t)qweight % 32 == 0) && ((uintptr_t)out % 16 == 0) && M < (1ll << 31) && IC < (1 << 24);
     if (fast) return launch_gemm_w2(x, qweight, scales, qzeros, out, M, IC, OC, group, zw, (cudaStream_t)stream, OC, 0, nullptr);
     // shapes the tcgen05 tile does not cover: stream the weights once per 8 rows through the GEMV kernel (correct, slow)
@@ -358,9 +358,9 @@ extern "C" int bdq_gemm_w2_tp(const void* x, const int32_t* qweight, const void*
         return BDQ_ERR_SHAPE;
     }
     const int zw = bdq_zeros_width(IC, group, 2);
-    const bool fast = zw >= 0 && (group == 128 || group == 64) && IC % 128 == 0 && OC_local % kGmN == 0 && ((uintptr_t)x % 16 == 0) &&
+    const bool fast = zw >= 0 && (group == 128 || group == 64) && IC % 128 == 0 && OC_local % 32 == 0 && ((uintptr_t)x % 16 == 0) &&
                       ((uintptr_t)qweight % 32 == 0) && ((uintptr_t)out % 16 == 0) && ldo % 8 == 0 && M < (1ll << 31) && IC < (1 << 24);
-    if (!fast) { set_error("gemm_w2_tp: needs group 64/128, IC %% 128 == 0, OC_local %% %d == 0", kGmN); return BDQ_ERR_UNSUPPORTED; }
+    if (!fast) { set_error("gemm_w2_tp: needs group 64/128, IC %% 128 == 0, OC_local %% 32 == 0"); return BDQ_ERR_UNSUPPORTED; }
     for (int i = 0; i < n_peer; ++i)
         if (!peer_out[i] || ((uintptr_t)peer_out[i] % 16)) { set_error("gemm_w2_tp: peer pointer %d null or misaligned", i); return BDQ_ERR_ALIGN; }
     return launch_gemm_w2(x, qweight, scales, qzeros, out, M, IC, OC_local, group, zw, (cudaStream_t)stream, ldo, n_peer, peer_out);

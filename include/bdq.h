@@ -148,7 +148,8 @@ int bdq_gemv_w2_multi(const void* x, int nmat, const int32_t* const* qweight, co
  * Replaces quant_matmul_v2 (quantization/triton_kernels.py:102-134) and gemm_forward_cuda (pybind.cpp:12; the
  * reference's CUDA GEMM is 4-bit only).  Operands are the row-major tensors WQLinear holds (qmodule.py:62-66) -- NOT the
  * transposed copies the reference builds per call (qmodule.py:154-158).  x [M, IC] fp16, out [M, OC] fp16.
- * Tensor-core path: group in {64, 128}, IC % 128 == 0, OC % 256 == 0; other shapes fall back to bdq_gemv_w2 row blocks.
+ * Tensor-core path: group in {64, 128}, IC % 128 == 0, OC % 32 == 0 (tiles are 256 channels wide, the last one may be
+ * partial); other shapes fall back to bdq_gemv_w2 row blocks.
  */
 int bdq_gemm_w2(const void* x, const int32_t* qweight, const void* scales, const int32_t* qzeros, void* out, int64_t M,
                 int64_t IC, int64_t OC, int group, bdq_stream_t stream);
@@ -162,7 +163,7 @@ int bdq_gemm_w2(const void* x, const int32_t* qweight, const void* scales, const
  * peer-mapped device addresses (e.g. torch symmetric memory `buffer_ptrs`).  The caller puts a cross-rank barrier between
  * these launches and the consumers of the gathered rows.
  *   bdq_gemv_w2_tp: batch-1 decode, up to 4 matrices sharing x (peer_out is [nmat][n_peer], row-major), group 128.
- *   bdq_gemm_w2_tp: prefill, output row pitch `ldo` elements (the full OC), tcgen05 shapes only (OC_local % 256 == 0).
+ *   bdq_gemm_w2_tp: prefill, output row pitch `ldo` elements (the full OC), tcgen05 shapes only (OC_local % 32 == 0).
  */
 int bdq_gemv_w2_tp(const void* x, int nmat, const int32_t* const* qweight, const void* const* scales,
                    const int32_t* const* qzeros, void* const* out, const int64_t* OC_local, int64_t IC, int group, int flags,

@@ -42,7 +42,8 @@ def _check(out, ref, x, dqw):
 
 
 @pytest.mark.parametrize("m,oc,ic,G", [(128, 256, 128, 128), (256, 512, 1024, 128), (2048, 4096, 4096, 128),
-                                       (200, 256, 11008, 128), (77, 1024, 4096, 128), (384, 512, 2048, 64)])
+                                       (200, 256, 11008, 128), (77, 1024, 4096, 128), (384, 512, 2048, 64),
+                                       (300, 128, 4096, 128), (130, 352, 1024, 128), (64, 64, 512, 128)])   # partial last N tile
 def test_gemm_w2_tcgen05_vs_reference_math(m, oc, ic, G):
     from bitdistiller_b200.triton_kernels import gemm_w2
     (qw, qz, qs), dq = _packed_layer(oc, ic, 5, G)
@@ -79,9 +80,9 @@ def test_wqlinear_prefill_and_quant_matmul_v2_convention():
 
 
 def test_gemm_w2_fallback_shapes():
-    """OC not a multiple of 256 takes the GEMV row-block fallback and still matches."""
+    """OC not a multiple of 32 takes the GEMV row-block fallback and still matches."""
     from bitdistiller_b200.triton_kernels import gemm_w2
-    (qw, qz, qs), dq = _packed_layer(64, 512, 3)
+    (qw, qz, qs), dq = _packed_layer(48, 512, 3)
     x = torch.randn(20, 512, generator=torch.Generator().manual_seed(1)).to(torch.float16).to(dev)
     out = gemm_w2(x, qw, qs, qz, 128)
     ref, dqw = _ref_gpu(x, qw, qz, qs, 128)

@@ -168,7 +168,7 @@ def bench_tp_fused(dev, rank, world, shards, ops, layers):
         rows1[oc].barrier()
         ok = ok and torch.equal(rows1[oc].t, ref)
         xm = torch.randn(256, ic, device=dev, generator=torch.Generator(device=dev).manual_seed(8)).half()
-        if sq.shape[0] % 256 == 0:
+        if sq.shape[0] % 32 == 0:
             refm = S.all_gather_cols(gemm_w2(xm, sq, ss, sz, 128))
             S.tp_gemm_fused(xm, (sq, ss, sz), rowsM[oc])
             rowsM[oc].barrier()
@@ -218,7 +218,7 @@ def bench_tp_fused(dev, rank, world, shards, ops, layers):
 
     def prefill():
         for sq, sz, ss, oc, ic in ops:
-            if sq.shape[0] % 256 == 0:
+            if sq.shape[0] % 32 == 0:
                 S.tp_gemm_fused(xm[ic], (sq, ss, sz), rowsM[oc])
                 rowsM[oc].barrier()
             else:
