@@ -142,7 +142,7 @@ __device__ __forceinline__ unsigned long long gtime() {
 // PROF: lane 0 of every warp records %globaltimer at the phase boundaries into prof[cta][warp][16] (dev tool only)
 template <bool PDL, bool PROF, bool TMA>
 __global__ void __launch_bounds__(kSThreads, 2) gemv_w2s_kernel(const __half* __restrict__ x, const GemvMats m, int IC,
-                                                                int zw, int total_rb, int wpw,
+                                                                int zw, int rb_q, int rb_r, int wpw,
                                                                 unsigned long long* __restrict__ prof, int xrep,
                                                                 const __grid_constant__ GemvMaps maps, int depth) {
     extern __shared__ __align__(128) uint8_t smem_raw[];
@@ -168,8 +168,38 @@ __global__ void __launch_bounds__(kSThreads, 2) gemv_w2s_kernel(const __half* __
     const int g = lane >> 2, t = lane & 3;
     const int ngrp = IC >> 7, nwin = (ngrp + 3) >> 2;
     const int row_bytes = IC >> 2, zw16 = zw * 16;
-    const int rb0 = (int)((int64_t)blockIdx.x * total_rb / gridDim.x);
-    const int rb1 = (int)((int64_t)(blockIdx.x + 1) * total_rb / gridDim.x);
+    // balanced contiguous split of the 16-channel blocks: the first (total_rb % grid) CTAs take one more (no division here)
+    const int rb0 = (int)blockIdx.x * rb_q + min((int)blockIdx.x, rb_r);
+    const int rb1 = rb0 + rb_q + ((int)blockIdx.x < rb_r ? 1 : 0);
+    // matrix lookup without dynamically indexed constant loads (those are dependent long-latency LDCs in the prologue)
+    // (the TMA variant has registers to spare and keeps everything in registers; the register-streaming variant is at
+    // its 128-register budget and indexes the parameter arrays instead)
+    int e0 = 0, e1 = 0, e2 = 0;
+    if constexpr (TMA) { e0 = m.rb_end[0]; e1 = m.rb_end[1]; e2 = m.rb_end[2]; }
+    auto mat_of = [&](int rb) {   // rb_end is non-decreasing
+        if constexpr (TMA) {
+            return (rb >= e0 ? 1 : 0) + (rb >= e1 ? 1 : 0) + (rb >= e2 ? 1 : 0);
+        } else {
+            int mi = 0;
+            while (mi < kMaxMats - 1 && rb >= m.rb_end[mi]) ++mi;
+            return mi;
+        }
+    };
+    auto rstart_of = [&](int mi) {
+        if constexpr (TMA) return mi == 0 ? 0 : (mi == 1 ? e0 : (mi == 2 ? e1 : e2));
+        else return mi ? m.rb_end[mi - 1] : 0;
+    };
+    const uint8_t *qw0 = nullptr, *qw1 = nullptr, *qw2 = nullptr, *qw3 = nullptr;
+    const __half *sc0 = nullptr, *sc1 = nullptr, *sc2 = nullptr, *sc3 = nullptr;
+    const uint32_t *qz0 = nullptr, *qz1 = nullptr, *qz2 = nullptr, *qz3 = nullptr;
+    if constexpr (TMA) {
+        qw0 = m.qw[0]; qw1 = m.qw[1]; qw2 = m.qw[2]; qw3 = m.qw[3];
+        sc0 = m.sc[0]; sc1 = m.sc[1]; sc2 = m.sc[2]; sc3 = m.sc[3];
+        qz0 = m.qz[0]; qz1 = m.qz[1]; qz2 = m.qz[2]; qz3 = m.qz[3];
+    }
+    auto qw_of = [&](int mi) { if constexpr (TMA) return mi == 0 ? qw0 : (mi == 1 ? qw1 : (mi == 2 ? qw2 : qw3)); else return m.qw[mi]; };
+    auto sc_of = [&](int mi) { if constexpr (TMA) return mi == 0 ? sc0 : (mi == 1 ? sc1 : (mi == 2 ? sc2 : sc3)); else return m.sc[mi]; };
+    auto qz_of = [&](int mi) { if constexpr (TMA) return mi == 0 ? qz0 : (mi == 1 ? qz1 : (mi == 2 ? qz2 : qz3)); else return m.qz[mi]; };
     const int mywin = warp < nwin ? (nwin - warp + kSWarps - 1) / kSWarps : 0;   // windows warp, warp+8, ...
     uint8_t* wbase = smem + (size_t)warp * gemv_s_warp_bytes(wpw);
     uint8_t* zblock = wbase + (size_t)wpw * kWinStride;
@@ -181,17 +211,16 @@ __global__ void __launch_bounds__(kSThreads, 2) gemv_w2s_kernel(const __half* __
     uint64_t* mbar = reinterpret_cast<uint64_t*>(meta + kRedSlots * meta_bytes) + kSWarps * 8;   // [kRedSlots]
     uint8_t* wring = ring + (size_t)warp * depth * kItemBytes;
     auto locate = [&](int rb, int& mi, int& r0) {   // 16-channel block -> (matrix, first channel)
-        mi = 0;
-        while (mi < kMaxMats - 1 && rb >= m.rb_end[mi]) ++mi;
-        r0 = (rb - (mi ? m.rb_end[mi - 1] : 0)) * 16;
+        mi = mat_of(rb);
+        r0 = (rb - rstart_of(mi)) * 16;
     };
     auto issue_meta = [&](int rb, int slot) {   // one thread: scales + zero words of block rb -> meta slot
         int mi, r0;
         locate(rb, mi, r0);
         uint8_t* dst = meta + slot * meta_bytes;
         gs_mbar_expect_tx(&mbar[slot], (uint32_t)meta_bytes);
-        gs_bulk_load(dst, m.sc[mi] + (size_t)r0 * zw16, 16 * zw * 32, &mbar[slot]);
-        gs_bulk_load(dst + 16 * zw * 32, m.qz[mi] + (size_t)r0 * zw, 16 * zw * 4, &mbar[slot]);
+        gs_bulk_load(dst, sc_of(mi) + (size_t)r0 * zw16, 16 * zw * 32, &mbar[slot]);
+        gs_bulk_load(dst + 16 * zw * 32, qz_of(mi) + (size_t)r0 * zw, 16 * zw * 4, &mbar[slot]);
     };
     int t_rb = rb0, t_j = 0, t_slot = 0;   // TMA producer cursor (lane 0 issues)
     auto issue_tma = [&]() {
@@ -222,32 +251,30 @@ __global__ void __launch_bounds__(kSThreads, 2) gemv_w2s_kernel(const __half* __
     }
 
     // ---- producer cursor: item = (16-channel block, window of this warp)
-    int p_rb = rb0, p_j = 0, p_mi = 0;
-    while (p_mi < kMaxMats - 1 && p_rb >= m.rb_end[p_mi]) ++p_mi;
+    int p_rb = rb0, p_j = 0, p_mi = mat_of(rb0);
     auto issue = [&](ItemBuf& b) {
         if (p_rb >= rb1) return;
-        const int rstart = p_mi ? m.rb_end[p_mi - 1] : 0;
-        const size_t r = (size_t)(p_rb - rstart) * 16 + g;
+        const size_t r = (size_t)(p_rb - rstart_of(p_mi)) * 16 + g;
         const int win = warp + kSWarps * p_j;
         const int G = 4 * win + t;
         if (G < ngrp) {
-            const uint8_t* pa = m.qw[p_mi] + r * row_bytes + (size_t)G * 32;
+            const uint8_t* pa = qw_of(p_mi) + r * row_bytes + (size_t)G * 32;
             b.a = ldg256(pa);
             b.b = ldg256(pa + (size_t)8 * row_bytes);
         } else {
 #pragma unroll
             for (int i = 0; i < 8; ++i) b.a.r[i] = b.b.r[i] = 0u;
         }
-        const __half* ps = m.sc[p_mi] + r * zw16 + G;   // G < zw16 always (scales are zero-padded to zw16 columns)
+        const __half* ps = sc_of(p_mi) + r * zw16 + G;   // G < zw16 always (scales are zero-padded to zw16 columns)
         b.sa = ldg_nc_u16(ps);
         b.sb = ldg_nc_u16(ps + (size_t)8 * zw16);
-        const uint32_t* pz = m.qz[p_mi] + r * zw + (G >> 4);
+        const uint32_t* pz = qz_of(p_mi) + r * zw + (G >> 4);
         b.za = ldg_nc_u32(pz);
         b.zb = ldg_nc_u32(pz + (size_t)8 * zw);
         if (++p_j == mywin) {
             p_j = 0;
             ++p_rb;
-            while (p_mi < kMaxMats - 1 && p_rb >= m.rb_end[p_mi]) ++p_mi;
+            p_mi = mat_of(p_rb);
         }
     };
     ItemBuf buf[TMA ? 1 : kDepth];
@@ -364,9 +391,8 @@ __global__ void __launch_bounds__(kSThreads, 2) gemv_w2s_kernel(const __half* __
 #pragma unroll
             for (int w = 0; w < kSWarps; ++w) acc += rp[w * 16];
             const int rb = rb_base + sl;
-            int mi = 0;
-            while (mi < kMaxMats - 1 && rb >= m.rb_end[mi]) ++mi;
-            const int rstart = mi ? m.rb_end[mi - 1] : 0;
+            const int mi = mat_of(rb);
+            const int rstart = rstart_of(mi);
             const __half hv = __float2half_rn(acc);
             const size_t oi = (size_t)(rb - rstart) * 16 + row;
             m.out[mi][oi] = hv;
@@ -588,7 +614,7 @@ int bdq_gemv_w2_stream_launch(const void* x, int nmat, const int32_t* const* qwe
         }
     }
     if (smem > 112 * 1024) return BDQ_ERR_UNSUPPORTED;   // two CTAs per SM
-    typedef void (*KernFn)(const __half*, const GemvMats, int, int, int, int, unsigned long long*, int, const GemvMaps, int);
+    typedef void (*KernFn)(const __half*, const GemvMats, int, int, int, int, int, unsigned long long*, int, const GemvMaps, int);
     static const KernFn kerns[8] = {gemv_w2s_kernel<false, false, false>, gemv_w2s_kernel<true, false, false>,
                                     gemv_w2s_kernel<false, true, false>,  gemv_w2s_kernel<true, true, false>,
                                     gemv_w2s_kernel<false, false, true>,  gemv_w2s_kernel<true, false, true>,
@@ -620,7 +646,7 @@ int bdq_gemv_w2_stream_launch(const void* x, int nmat, const int32_t* const* qwe
         g_gemv_prof_used += (size_t)grid * kSWarps * 16;
         if (g_gemv_prof_used > g_gemv_prof_cap) return BDQ_ERR_SHAPE;
     }
-    cudaLaunchKernelEx(&cfg, kern, (const __half*)x, m, (int)IC, zw, total_rb, wpw, pbuf, prof ? ((flags >> 8) & 0xff) + 1 : 1,
+    cudaLaunchKernelEx(&cfg, kern, (const __half*)x, m, (int)IC, zw, total_rb / grid, total_rb % grid, wpw, pbuf, prof ? ((flags >> 8) & 0xff) + 1 : 1,
                        maps, depth);
     return check_launch("bdq_gemv_w2(stream)");
 }

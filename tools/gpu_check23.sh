@@ -1,0 +1,4 @@
+#!/bin/bash
+timeout 900 python -m pytest tests/test_packed_gpu.py -m gpu -x -q 2>&1 | tail -2
+timeout 600 python tools/bench_gemv.py 1 2>&1 | grep "fused\|best" | grep -v ring
+echo "=== layer"; timeout 300 python tools/gemv_timeline.py layer 1 2>&1 | tail -5
