@@ -7,9 +7,11 @@
 //   * the straight-through value (y - q).detach() + q = rT(rT(lvl - q) + q) equals lvl for EVERY T value q in [-1, 1]
 //     (checked exhaustively for bf16 and fp16: all levels satisfy Sterbenz' condition on their own interval), so the
 //     forward output is  rT(lvl(x) * s): a step function of x with 7 thresholds and 8 per-group output values.
-// Each x-space threshold T_k = min{ x : rT(x / s) >= thr_k } is found per group by evaluating the exact predicate on
-// the 5 neighbouring T values around rT(thr_k * s) and accepted only if the predicate flips inside that window;
-// otherwise the group takes the op-by-op path (nf3_elem).  The per-element work is 7 packed compares + 7 selects.
+// Each x-space threshold T_k = min{ x : rT(x / s) >= thr_k } is computed per group from the exact product (midpoint below
+// thr_k) * s and verified with the op-by-op predicate at the candidate and its predecessor; a group whose candidate
+// fails the check takes the op-by-op path (nf3_elem).  The per-element work is 7 packed compares + 7 selects.
+#include <cstring>
+
 #include "fakequant_thr.cuh"
 #include "fq_nf3_elem.cuh"
 
@@ -24,33 +26,55 @@ __device__ __forceinline__ uint32_t nf3_group_lane_mask(int lane) {
 
 // ascending staircase: k = 0..2 negative thresholds (neg_thr[2], [1], [0]) on x / sn, k = 3..6 positive ones on x / sp
 struct Nf3Stair {
+    float mid[7];   // midpoint between thr[k] and the next T value below it (exact in fp32)
+    int incl[7];    // 1: thr[k] has an even significand, a quotient exactly at the midpoint rounds up to it
     float thr[7];   // in q space, rounded to T
     float lvl[8];   // level values in q space, rounded to T: -1, neg_lvl[2], neg_lvl[1], 0, pos_lvl[1..4]
 };
 
-static Nf3Stair make_stair(const Nf3Tables& t) {
+static float host_prev_T(float v, int dt, int* even) {   // next T value below v (v != 0), and whether v's significand is even
+    uint32_t b;
+    memcpy(&b, &v, 4);
+    const int sh = (dt == kBF16) ? 16 : 13;   // fp32 bits below the T significand (fp16 normal range; |thr| > 2^-14)
+    *even = ((b >> sh) & 1u) == 0u;
+    const uint32_t step = 1u << sh;
+    b = (v > 0.f) ? b - step : b + step;      // towards -inf: magnitude down for positive, up for negative
+    float r;
+    memcpy(&r, &b, 4);
+    return r;
+}
+
+static Nf3Stair make_stair(const Nf3Tables& t, int dt) {
     Nf3Stair s;
     s.thr[0] = t.neg_thr[2]; s.thr[1] = t.neg_thr[1]; s.thr[2] = t.neg_thr[0];
     for (int i = 0; i < 4; ++i) s.thr[3 + i] = t.pos_thr[i];
     s.lvl[0] = t.neg_lvl[3]; s.lvl[1] = t.neg_lvl[2]; s.lvl[2] = t.neg_lvl[1]; s.lvl[3] = 0.f;
     for (int i = 1; i < 5; ++i) s.lvl[3 + i] = t.pos_lvl[i];
+    for (int k = 0; k < 7; ++k) {
+        int even;
+        const float pv = host_prev_T(s.thr[k], dt, &even);
+        s.mid[k] = 0.5f * (s.thr[k] + pv);    // exact: adjacent T values
+        s.incl[k] = even;
+    }
     return s;
 }
 
-// smallest T value x (of the sign of thr) with rT(x / s) >= thr; ok = false if not bracketed by the 5-point window
+// smallest T value x with rT(x / s) >= thr.  rT(x / s) >= thr  <=>  x / s >= mid (or > mid), mid = the midpoint between
+// thr and its predecessor in T, so the threshold is the smallest T value >= (>) mid * s -- a product that is exact in fp32
+// (<= 12 x 11 significant bits).  `incl` = thr has an even significand (a tie at the midpoint rounds to thr).  The
+// candidate is then VERIFIED with the exact op-by-op predicate at the candidate and at its predecessor; ok = false sends
+// the group to the op-by-op path, so exactness does not rest on the argument above.
 template <int DT>
-__device__ __forceinline__ float nf3_find_threshold(float thr, float s, float y, bool& ok) {
-    const float xc = rT<DT>(thr * s);
-    uint32_t pm = 0;
-#pragma unroll
-    for (int j = 0; j < 5; ++j) {
-        const float x = t_step<DT>(xc, j - 2);
-        const float q = rT<DT>(div_exact<DT>(x, s, y));
-        pm |= (q >= thr ? 1u : 0u) << j;
-    }
-    const int i = __ffs(pm) - 1;
-    ok = (i >= 1) && (pm == ((0x1fu << i) & 0x1fu)) && (xc != 0.f);
-    return t_step<DT>(xc, i - 2);
+__device__ __forceinline__ float nf3_find_threshold(float thr, float mid, bool incl, float s, float y, bool& ok) {
+    const float v = mid * s;
+    float c = rT<DT>(v);
+    if (incl ? (c < v) : (c <= v)) c = t_step<DT>(c, 1);
+    const float cp = t_step<DT>(c, -1);
+    float q0;
+    const bool pc = rT<DT>(div_fast(c, s, y, q0)) >= thr;
+    const bool pp = rT<DT>(div_fast(cp, s, y, q0)) >= thr;
+    ok = pc && !pp && (c != 0.f) && (cp != 0.f);
+    return c;
 }
 
 template <int DT>
@@ -116,7 +140,7 @@ __global__ void __launch_bounds__(kNf3ThrThreads) nf3_thr_fwd_kernel(const uint8
             tl[r] = 0.f;
             if (k < 7) {
                 bool o;
-                tl[r] = nf3_find_threshold<DT>(st.thr[k], k < 3 ? p.sn : p.sp, k < 3 ? p.yn : p.yp, o);
+                tl[r] = nf3_find_threshold<DT>(st.thr[k], st.mid[k], st.incl[k] != 0, k < 3 ? p.sn : p.sp, k < 3 ? p.yn : p.yp, o);
                 ok = ok && o;
             }
         }
@@ -166,7 +190,7 @@ template <int DT, bool CLIP>
 static void nf3_thr_fwd_g(const uint8_t* w, uint8_t* dq, const void* cmin, const void* cmax, int64_t nchunk, int G,
                           const Nf3Tables& tab, cudaStream_t st) {
     const int grid = nf3_thr_grid(nchunk);
-    const Nf3Stair stair = make_stair(tab);
+    const Nf3Stair stair = make_stair(tab, DT);
     if (G == 128) nf3_thr_fwd_kernel<DT, 128, CLIP><<<grid, kNf3ThrThreads, 0, st>>>(w, dq, cmin, cmax, nchunk, tab, stair);
     else if (G == 64) nf3_thr_fwd_kernel<DT, 64, CLIP><<<grid, kNf3ThrThreads, 0, st>>>(w, dq, cmin, cmax, nchunk, tab, stair);
     else nf3_thr_fwd_kernel<DT, 32, CLIP><<<grid, kNf3ThrThreads, 0, st>>>(w, dq, cmin, cmax, nchunk, tab, stair);
