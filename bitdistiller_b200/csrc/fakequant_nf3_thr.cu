@@ -8,8 +8,11 @@
 //     (checked exhaustively for bf16 and fp16: all levels satisfy Sterbenz' condition on their own interval), so the
 //     forward output is  rT(lvl(x) * s): a step function of x with 7 thresholds and 8 per-group output values.
 // Each x-space threshold T_k = min{ x : rT(x / s) >= thr_k } is computed per group from the exact product (midpoint below
-// thr_k) * s and verified with the op-by-op predicate at the candidate and its predecessor; a group whose candidate
-// fails the check takes the op-by-op path (nf3_elem).  The per-element work is 7 packed compares + 7 selects.
+// thr_k) * s and then verified: with the fp32 quotient computed exactly as the op-by-op path computes it, the candidate
+// must satisfy rT(q) >= thr_k and the T value just below it must not (rT(q) >= thr_k is tested as q >= midx, which is
+// what round-to-nearest-even means).  A group whose candidate fails the check takes the op-by-op path (nf3_elem), so
+// exactness never rests on the guess.  The per-element work is 7 packed compares + 7 selects, both on the ALU pipe,
+// which bounds this kernel (ncu: ALU pipe 84 % active at 78 % of the HBM peak before the per-group work was trimmed).
 #include <cstring>
 
 #include "fakequant_thr.cuh"
@@ -24,61 +27,60 @@ __device__ __forceinline__ uint32_t nf3_group_lane_mask(int lane) {
     return ((LPG == 32) ? 0xffffffffu : ((1u << LPG) - 1u)) << (lane & ~(LPG - 1));
 }
 
-// ascending staircase: k = 0..2 negative thresholds (neg_thr[2], [1], [0]) on x / sn, k = 3..6 positive ones on x / sp
+// ascending staircase: k = 0..2 negative thresholds (neg_thr[2], [1], [0]) on x / sn, k = 3..6 positive ones on x / sp.
+// Per threshold thr (a T value; prev = the next T value below it, mid = their midpoint, exact in fp32):
+//   rT(q) >= thr  <=>  q >= midx,   midx = mid if thr has an even significand (a tie rounds up to thr), else the next
+//   fp32 value above mid -- plain round-to-nearest-even, no assumption about the data.
+struct Nf3Step {
+    float mid;       // candidate: smallest T value >= (or >) mid * s, computed on the fp32 bit pattern as
+    float midx;      //   c = (bits(mid * s) + add) & mask   (ceil for positive values, truncation for negative ones)
+    uint32_t add;
+    int32_t pstep;   // bits(c) + pstep = the T value just below c
+};
 struct Nf3Stair {
-    float mid[7];   // midpoint between thr[k] and the next T value below it (exact in fp32)
-    int incl[7];    // 1: thr[k] has an even significand, a quotient exactly at the midpoint rounds up to it
-    float thr[7];   // in q space, rounded to T
-    float lvl[8];   // level values in q space, rounded to T: -1, neg_lvl[2], neg_lvl[1], 0, pos_lvl[1..4]
+    Nf3Step k[8];      // k[7]: dummy that always verifies (mid = midx = 1)
+    uint32_t lvl2[8];  // level values as packed T pairs: -1, neg_lvl[2], neg_lvl[1], 0, pos_lvl[1..4]
+    uint32_t mask;     // keeps the T significand of an fp32 pattern
 };
 
-static float host_prev_T(float v, int dt, int* even) {   // next T value below v (v != 0), and whether v's significand is even
-    uint32_t b;
-    memcpy(&b, &v, 4);
-    const int sh = (dt == kBF16) ? 16 : 13;   // fp32 bits below the T significand (fp16 normal range; |thr| > 2^-14)
-    *even = ((b >> sh) & 1u) == 0u;
-    const uint32_t step = 1u << sh;
-    b = (v > 0.f) ? b - step : b + step;      // towards -inf: magnitude down for positive, up for negative
-    float r;
-    memcpy(&r, &b, 4);
-    return r;
-}
+static uint32_t host_f2u(float v) { uint32_t b; memcpy(&b, &v, 4); return b; }
+static float host_u2f(uint32_t b) { float v; memcpy(&v, &b, 4); return v; }
 
 static Nf3Stair make_stair(const Nf3Tables& t, int dt) {
     Nf3Stair s;
-    s.thr[0] = t.neg_thr[2]; s.thr[1] = t.neg_thr[1]; s.thr[2] = t.neg_thr[0];
-    for (int i = 0; i < 4; ++i) s.thr[3 + i] = t.pos_thr[i];
-    s.lvl[0] = t.neg_lvl[3]; s.lvl[1] = t.neg_lvl[2]; s.lvl[2] = t.neg_lvl[1]; s.lvl[3] = 0.f;
-    for (int i = 1; i < 5; ++i) s.lvl[3 + i] = t.pos_lvl[i];
+    const int sh = (dt == kBF16) ? 16 : 13;   // fp32 bits below the T significand (fp16: normal range only, |thr| > 2^-14)
+    const uint32_t step = 1u << sh;
+    s.mask = ~(step - 1u);
+    float thr[7], lvl[8];
+    thr[0] = t.neg_thr[2]; thr[1] = t.neg_thr[1]; thr[2] = t.neg_thr[0];
+    for (int i = 0; i < 4; ++i) thr[3 + i] = t.pos_thr[i];
+    lvl[0] = t.neg_lvl[3]; lvl[1] = t.neg_lvl[2]; lvl[2] = t.neg_lvl[1]; lvl[3] = 0.f;
+    for (int i = 1; i < 5; ++i) lvl[3 + i] = t.pos_lvl[i];
     for (int k = 0; k < 7; ++k) {
-        int even;
-        const float pv = host_prev_T(s.thr[k], dt, &even);
-        s.mid[k] = 0.5f * (s.thr[k] + pv);    // exact: adjacent T values
-        s.incl[k] = even;
+        const uint32_t b = host_f2u(thr[k]);
+        const bool neg = thr[k] < 0.f;
+        const bool even = ((b >> sh) & 1u) == 0u;
+        const float prev = host_u2f(neg ? b + step : b - step);   // towards -inf
+        const float mid = 0.5f * (thr[k] + prev);                 // exact: adjacent T values
+        s.k[k].mid = mid;
+        s.k[k].midx = even ? mid : nextafterf(mid, INFINITY);
+        s.k[k].add = neg ? (even ? 0u : 0xffffffffu) : (even ? step - 1u : step);
+        s.k[k].pstep = neg ? (int32_t)step : -(int32_t)step;
+    }
+    s.k[7].mid = 1.f; s.k[7].midx = 1.f; s.k[7].add = 0u; s.k[7].pstep = -(int32_t)step;
+    for (int c = 0; c < 8; ++c) {
+        uint32_t h;
+        if (dt == kBF16) h = host_f2u(lvl[c]) >> 16;
+        else { const __half hv = __float2half_rn(lvl[c]); unsigned short u; memcpy(&u, &hv, 2); h = u; }
+        s.lvl2[c] = h | (h << 16);
     }
     return s;
 }
 
-// smallest T value x with rT(x / s) >= thr.  rT(x / s) >= thr  <=>  x / s >= mid (or > mid), mid = the midpoint between
-// thr and its predecessor in T, so the threshold is the smallest T value >= (>) mid * s -- a product that is exact in fp32
-// (<= 12 x 11 significant bits).  `incl` = thr has an even significand (a tie at the midpoint rounds to thr).  The
-// candidate is then VERIFIED with the exact op-by-op predicate at the candidate and at its predecessor; ok = false sends
-// the group to the op-by-op path, so exactness does not rest on the argument above.
 template <int DT>
-__device__ __forceinline__ float nf3_find_threshold(float thr, float mid, bool incl, float s, float y, bool& ok) {
-    const float v = mid * s;
-    float c = rT<DT>(v);
-    if (incl ? (c < v) : (c <= v)) c = t_step<DT>(c, 1);
-    const float cp = t_step<DT>(c, -1);
-    float q0;
-    const bool pc = rT<DT>(div_fast(c, s, y, q0)) >= thr;
-    const bool pp = rT<DT>(div_fast(cp, s, y, q0)) >= thr;
-    ok = pc && !pp && (c != 0.f) && (cp != 0.f);
-    return c;
-}
-
-template <int DT>
-__device__ __noinline__ void nf3_fwd_slow_global(const void* w, void* dq, int64_t e0, float lo, float hi, Nf3Q p, Nf3Tables t) {
+__device__ __noinline__ void nf3_fwd_slow_global(const void* w, void* dq, int64_t e0, float lo, float hi, float mx, float mn,
+                                                 const Nf3Tables& t) {
+    const Nf3Q p = nf3_group_params(mx, mn);
 #pragma unroll 1
     for (int i = 0; i < 32; ++i) {
         const float x = fminf(fmaxf(load_scalar<DT>(w, e0 + i), lo), hi);
@@ -91,16 +93,22 @@ __device__ __noinline__ void nf3_fwd_slow_global(const void* w, void* dq, int64_
 template <int DT, int G, bool CLIP>
 __global__ void __launch_bounds__(kNf3ThrThreads) nf3_thr_fwd_kernel(const uint8_t* __restrict__ w, uint8_t* __restrict__ dq,
                                                                      const void* __restrict__ cmin, const void* __restrict__ cmax,
-                                                                     int64_t nchunk, const Nf3Tables tab, const Nf3Stair st) {
+                                                                     int64_t nchunk, const __grid_constant__ Nf3Tables tab,
+                                                                     const __grid_constant__ Nf3Stair st) {
     using P = P2<DT>;
     using h2 = typename P::h2;
     constexpr int LPG = G / 32;
-    constexpr int R = (7 + LPG - 1) / LPG;
+    constexpr int R = (7 + LPG - 1) / LPG;   // thresholds found per lane
+    constexpr int NP = (R + 1) / 2;          // ... packed two per register
     const int lane = threadIdx.x & 31;
     const int lig = lane & (LPG - 1);
+    const int gbase = lane & ~(LPG - 1);
     const int64_t warp = (int64_t)blockIdx.x * (kNf3ThrThreads / 32) + (threadIdx.x >> 5);
     const int64_t nwarps = (int64_t)gridDim.x * (kNf3ThrThreads / 32);
     const int64_t nwc = (nchunk + 31) / 32;
+    Nf3Step my[R];   // this lane's thresholds: k = lig + r * LPG (k == 7, one lane per group: the always-true dummy)
+#pragma unroll
+    for (int r = 0; r < R; ++r) my[r] = st.k[lig + r * LPG];
     for (int64_t wc = warp; wc < nwc; wc += nwarps) {
         const int64_t idx = wc * 32 + lane;
         const bool valid = idx < nchunk;
@@ -130,30 +138,45 @@ __global__ void __launch_bounds__(kNf3ThrThreads) nf3_thr_fwd_kernel(const uint8
         vec_minmax16<DT>(raw[1], mx1, mn1);
         mx = group_max<LPG>(fmaxf(mx, mx1));
         mn = group_min<LPG>(fminf(mn, mn1));
-        const Nf3Q p = nf3_group_params(mx, mn);
-        // thresholds of this lane's group: one (or R) per lane, then broadcast
-        float tl[R];
-        bool ok = !p.nan_group && (p.sp * p.yp > 0.5f) && (p.sn * p.yn > 0.5f) && (p.yp < 1e30f) && (p.yn < 1e30f);
+        const float sp = fabsf(mx), sn = fabsf(mn);
+        const float yp = rcp_approx(sp), yn = rcp_approx(sn);
+        // scales in a range where the reciprocal is sane and (fp16) every candidate is a normal T value; a zero scale
+        // (NaN group), NaN or inf fails these compares
+        constexpr float kLo = (DT == kBF16) ? 1e-30f : 0.001953125f;   // 2^-9
+        bool ok = (sp >= kLo) && (sp < 1e30f) && (sn >= kLo) && (sn < 1e30f);
+        // thresholds of this lane's group: R per lane, verified, packed in pairs, then broadcast
+        float tl[2 * NP];
+#pragma unroll
+        for (int r = 0; r < 2 * NP; ++r) tl[r] = 0.f;
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            const int k = lig + r * LPG;
-            tl[r] = 0.f;
-            if (k < 7) {
-                bool o;
-                tl[r] = nf3_find_threshold<DT>(st.thr[k], st.mid[k], st.incl[k] != 0, k < 3 ? p.sn : p.sp, k < 3 ? p.yn : p.yp, o);
-                ok = ok && o;
-            }
+            const Nf3Step e = my[r];
+            const bool neg = lig + r * LPG < 3;
+            const float s = neg ? sn : sp, y = neg ? yn : yp;
+            const uint32_t cb = (__float_as_uint(e.mid * s) + e.add) & st.mask;
+            const float c = __uint_as_float(cb), cprev = __uint_as_float(cb + (uint32_t)e.pstep);
+            float q0;
+            const bool pc = div_fast(c, s, y, q0) >= e.midx;
+            const bool pp = div_fast(cprev, s, y, q0) >= e.midx;
+            ok = ok && pc && !pp;
+            tl[r] = c;
         }
+        uint32_t pk[NP], sh[LPG][NP];
+#pragma unroll
+        for (int j = 0; j < NP; ++j) pk[j] = P::bits(P::pack(tl[2 * j], tl[2 * j + 1]));   // exact: T values
+#pragma unroll
+        for (int l = 0; l < LPG; ++l)
+#pragma unroll
+            for (int j = 0; j < NP; ++j) sh[l][j] = (LPG == 1) ? pk[j] : __shfl_sync(0xffffffffu, pk[j], gbase + l);
         const uint32_t okm = __ballot_sync(0xffffffffu, ok);
         const uint32_t gm = nf3_group_lane_mask<LPG>(lane);
         const bool fast = (okm & gm) == gm;
         if (fast) {
-            uint32_t t2[7], v2[8];
+            const h2 s2p = P::dup(sp), s2n = P::dup(sn);
+            uint32_t v2[8];
 #pragma unroll
-            for (int k = 0; k < 7; ++k)
-                t2[k] = P::bits(P::dup(__shfl_sync(0xffffffffu, tl[k / LPG], (lane & ~(LPG - 1)) + (k % LPG))));
-#pragma unroll
-            for (int c = 0; c < 8; ++c) v2[c] = P::bits(P::dup(st.lvl[c] * (c < 3 ? p.sn : p.sp)));   // rT(lvl * s)
+            for (int c = 0; c < 8; ++c)   // rT(lvl * s): one rounding of an exact product either way
+                v2[c] = (c == 3) ? 0u : P::bits(__hmul2(P::from_bits(st.lvl2[c]), c < 3 ? s2n : s2p));
             U8 out[2];
 #pragma unroll
             for (int v = 0; v < 2; ++v)
@@ -163,7 +186,9 @@ __global__ void __launch_bounds__(kNf3ThrThreads) nf3_thr_fwd_kernel(const uint8
                     uint32_t o = v2[0];
 #pragma unroll
                     for (int k = 0; k < 7; ++k) {
-                        const uint32_t m = __hge2_mask(x2, P::from_bits(t2[k]));
+                        const h2 tk = P::from_bits(sh[k % LPG][(k / LPG) / 2]);
+                        const h2 t2 = ((k / LPG) & 1) ? P::dup_hi(tk) : P::dup_lo(tk);
+                        const uint32_t m = __hge2_mask(x2, t2);
                         asm("lop3.b32 %0, %1, %2, %3, 0xCA;" : "=r"(o) : "r"(m), "r"(v2[k + 1]), "r"(o));   // m ? v : o
                     }
                     out[v].r[i] = o;
@@ -173,7 +198,7 @@ __global__ void __launch_bounds__(kNf3ThrThreads) nf3_thr_fwd_kernel(const uint8
                 stg256(dq + idx * 64 + 32, out[1]);
             }
         } else if (valid) {
-            nf3_fwd_slow_global<DT>(w, dq, idx * 32, clo, chi, p, tab);
+            nf3_fwd_slow_global<DT>(w, dq, idx * 32, clo, chi, mx, mn, tab);
         }
     }
 }

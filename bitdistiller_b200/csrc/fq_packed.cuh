@@ -26,6 +26,8 @@ struct P2<kBF16> {
     static __device__ __forceinline__ uint32_t bits(h2 v) { return *reinterpret_cast<uint32_t*>(&v); }
     static __device__ __forceinline__ h2 pack(float a, float b) { return __floats2bfloat162_rn(a, b); }
     static __device__ __forceinline__ h2 dup(float a) { return __float2bfloat162_rn(a); }
+    static __device__ __forceinline__ h2 dup_lo(h2 v) { return __low2bfloat162(v); }
+    static __device__ __forceinline__ h2 dup_hi(h2 v) { return __high2bfloat162(v); }
     static __device__ __forceinline__ float lo(h2 v) { return __uint_as_float(bits(v) << 16); }
     static __device__ __forceinline__ float hi(h2 v) { return __uint_as_float(bits(v) & 0xffff0000u); }
     static constexpr float kRoundC = 0.5f + 0.001953125f;  // 0.5 + 2^-9
@@ -38,6 +40,8 @@ struct P2<kF16> {
     static __device__ __forceinline__ uint32_t bits(h2 v) { return *reinterpret_cast<uint32_t*>(&v); }
     static __device__ __forceinline__ h2 pack(float a, float b) { return __floats2half2_rn(a, b); }
     static __device__ __forceinline__ h2 dup(float a) { return __float2half2_rn(a); }
+    static __device__ __forceinline__ h2 dup_lo(h2 v) { return __low2half2(v); }
+    static __device__ __forceinline__ h2 dup_hi(h2 v) { return __high2half2(v); }
     static __device__ __forceinline__ float lo(h2 v) { return __low2float(v); }
     static __device__ __forceinline__ float hi(h2 v) { return __high2float(v); }
     static constexpr float kRoundC = 0.5f + 0.000244140625f;  // 0.5 + 2^-12

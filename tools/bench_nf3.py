@@ -1,0 +1,49 @@
+"""NF3 (BASELINE config 3) fake-quant timing on one Llama-2-7B decoder layer's flat bf16 parameter buffer (202.4 M
+weights = bench.py's launch shape): forward with and without the fused clip, STE backward.  CUDA events, 3 rotating
+buffers (1.2 GB >> L2), median of 20."""
+import json
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from bitdistiller_b200 import _lib as L  # noqa: E402
+from microbench import timeit  # noqa: E402
+
+
+def main():
+    dev = torch.device("cuda:0")
+    peak = json.load(open(os.path.join(os.path.dirname(__file__), "..", "MEASURED_PEAKS.json"))).get("hbm_gbs", 6553.3) \
+        if os.path.exists(os.path.join(os.path.dirname(__file__), "..", "MEASURED_PEAKS.json")) else 6553.3
+    N = 4 * 4096 * 4096 + 3 * 11008 * 4096
+    nbuf = 3
+    ws = [(torch.randn(N, device=dev) * 0.02).to(torch.bfloat16) for _ in range(nbuf)]
+    gs = [torch.randn(N, device=dev).to(torch.bfloat16) for _ in range(nbuf)]
+    out = torch.empty_like(ws[0])
+    ng = N // 128
+    cmax = [(w.view(ng, 128).amax(1) * 0.8).contiguous() for w in ws]
+    cmin = [(w.view(ng, 128).amin(1) * 0.85).contiguous() for w in ws]
+    lib, st, n = L.lib(), L.stream_ptr(dev), L.i64(N)
+
+    def nfwd(i):
+        lib.bdq_nf3_fakequant_fwd(L.ptr(ws[i]), L.ptr(out), None, None, None, None, None, n, 128, 1, 0, st)
+
+    def nclip(i):
+        lib.bdq_nf3_fakequant_fwd(L.ptr(ws[i]), L.ptr(out), None, None, None, L.ptr(cmin[i]), L.ptr(cmax[i]), n, 128, 1, 0, st)
+
+    def nbwd(i):
+        lib.bdq_nf3_ste_bwd(L.ptr(ws[i]), L.ptr(gs[i]), L.ptr(out), n, 128, 1, 0, st)
+
+    def ifwd(i):
+        lib.bdq_int_fakequant_fwd(L.ptr(ws[i]), L.ptr(out), None, None, None, None, None, n, 128, 2, 1, 1, 0, st)
+
+    for name, fn, bpw in [("int2 fwd", ifwd, 4), ("nf3 fwd", nfwd, 4), ("nf3 fwd + clip (config 3)", nclip, 4 + 4 / 128),
+                          ("nf3 ste bwd", nbwd, 6)]:
+        t = timeit(fn, nbuf)
+        gbs = N * bpw / t / 1e9
+        print(f"bf16 flat layer {name:28s} {t*1e6:8.1f} us  {gbs:7.1f} GB/s  {gbs/peak*100:5.1f}% of HBM peak ({peak:.0f})")
+
+
+if __name__ == "__main__":
+    main()
