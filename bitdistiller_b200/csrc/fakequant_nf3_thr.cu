@@ -77,6 +77,64 @@ static Nf3Stair make_stair(const Nf3Tables& t, int dt) {
     return s;
 }
 
+// Thresholds of the lane's group (scales sp, sn): every lane finds and verifies R of the 7 (my[r]: k = lig + r * LPG),
+// packs them in pairs and the group's lanes exchange them: threshold k ends up in sh[k % LPG][(k / LPG) / 2], half
+// (k / LPG) & 1, on every lane of the group.  Returns this lane's verdict (all of the group's lanes must agree).
+template <int DT, int LPG>
+__device__ __forceinline__ bool nf3_group_thresholds(const Nf3Step (&my)[(7 + LPG - 1) / LPG], uint32_t mask, float sp, float sn,
+                                                     int lig, int gbase, uint32_t (&sh)[LPG][((7 + LPG - 1) / LPG + 1) / 2]) {
+    using P = P2<DT>;
+    constexpr int R = (7 + LPG - 1) / LPG;
+    constexpr int NP = (R + 1) / 2;
+    const float yp = rcp_approx(sp), yn = rcp_approx(sn);
+    // scales in a range where the reciprocal is sane and (fp16) every candidate is a normal T value; a zero scale
+    // (NaN group), NaN or inf fails these compares
+    constexpr float kLo = (DT == kBF16) ? 1e-30f : 0.001953125f;   // 2^-9
+    bool ok = (sp >= kLo) && (sp < 1e30f) && (sn >= kLo) && (sn < 1e30f);
+    float tl[2 * NP];
+#pragma unroll
+    for (int r = 0; r < 2 * NP; ++r) tl[r] = 0.f;
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const Nf3Step e = my[r];
+        const bool neg = lig + r * LPG < 3;
+        const float s = neg ? sn : sp, y = neg ? yn : yp;
+        const uint32_t cb = (__float_as_uint(e.mid * s) + e.add) & mask;
+        const float c = __uint_as_float(cb), cprev = __uint_as_float(cb + (uint32_t)e.pstep);
+        float q0;
+        const bool pc = div_fast(c, s, y, q0) >= e.midx;
+        const bool pp = div_fast(cprev, s, y, q0) >= e.midx;
+        ok = ok && pc && !pp;
+        tl[r] = c;
+    }
+    uint32_t pk[NP];
+#pragma unroll
+    for (int j = 0; j < NP; ++j) pk[j] = P::bits(P::pack(tl[2 * j], tl[2 * j + 1]));   // exact: T values
+#pragma unroll
+    for (int l = 0; l < LPG; ++l)
+#pragma unroll
+        for (int j = 0; j < NP; ++j) sh[l][j] = (LPG == 1) ? pk[j] : __shfl_sync(0xffffffffu, pk[j], gbase + l);
+    return ok;
+}
+
+// packed level select: 7 compares + 7 bit-selects per pair; v2[c] = the output value of level c (packed pair)
+template <int DT, int LPG>
+__device__ __forceinline__ uint32_t nf3_select(uint32_t x, const uint32_t (&sh)[LPG][((7 + LPG - 1) / LPG + 1) / 2],
+                                               const uint32_t (&v2)[8]) {
+    using P = P2<DT>;
+    using h2 = typename P::h2;
+    const h2 x2 = P::from_bits(x);
+    uint32_t o = v2[0];
+#pragma unroll
+    for (int k = 0; k < 7; ++k) {
+        const h2 tk = P::from_bits(sh[k % LPG][(k / LPG) / 2]);
+        const h2 t2 = ((k / LPG) & 1) ? P::dup_hi(tk) : P::dup_lo(tk);
+        const uint32_t m = __hge2_mask(x2, t2);
+        asm("lop3.b32 %0, %1, %2, %3, 0xCA;" : "=r"(o) : "r"(m), "r"(v2[k + 1]), "r"(o));   // m ? v : o
+    }
+    return o;
+}
+
 template <int DT>
 __device__ __noinline__ void nf3_fwd_slow_global(const void* w, void* dq, int64_t e0, float lo, float hi, float mx, float mn,
                                                  const Nf3Tables& t) {
@@ -139,35 +197,8 @@ __global__ void __launch_bounds__(kNf3ThrThreads) nf3_thr_fwd_kernel(const uint8
         mx = group_max<LPG>(fmaxf(mx, mx1));
         mn = group_min<LPG>(fminf(mn, mn1));
         const float sp = fabsf(mx), sn = fabsf(mn);
-        const float yp = rcp_approx(sp), yn = rcp_approx(sn);
-        // scales in a range where the reciprocal is sane and (fp16) every candidate is a normal T value; a zero scale
-        // (NaN group), NaN or inf fails these compares
-        constexpr float kLo = (DT == kBF16) ? 1e-30f : 0.001953125f;   // 2^-9
-        bool ok = (sp >= kLo) && (sp < 1e30f) && (sn >= kLo) && (sn < 1e30f);
-        // thresholds of this lane's group: R per lane, verified, packed in pairs, then broadcast
-        float tl[2 * NP];
-#pragma unroll
-        for (int r = 0; r < 2 * NP; ++r) tl[r] = 0.f;
-#pragma unroll
-        for (int r = 0; r < R; ++r) {
-            const Nf3Step e = my[r];
-            const bool neg = lig + r * LPG < 3;
-            const float s = neg ? sn : sp, y = neg ? yn : yp;
-            const uint32_t cb = (__float_as_uint(e.mid * s) + e.add) & st.mask;
-            const float c = __uint_as_float(cb), cprev = __uint_as_float(cb + (uint32_t)e.pstep);
-            float q0;
-            const bool pc = div_fast(c, s, y, q0) >= e.midx;
-            const bool pp = div_fast(cprev, s, y, q0) >= e.midx;
-            ok = ok && pc && !pp;
-            tl[r] = c;
-        }
-        uint32_t pk[NP], sh[LPG][NP];
-#pragma unroll
-        for (int j = 0; j < NP; ++j) pk[j] = P::bits(P::pack(tl[2 * j], tl[2 * j + 1]));   // exact: T values
-#pragma unroll
-        for (int l = 0; l < LPG; ++l)
-#pragma unroll
-            for (int j = 0; j < NP; ++j) sh[l][j] = (LPG == 1) ? pk[j] : __shfl_sync(0xffffffffu, pk[j], gbase + l);
+        uint32_t sh[LPG][NP];
+        const bool ok = nf3_group_thresholds<DT, LPG>(my, st.mask, sp, sn, lig, gbase, sh);
         const uint32_t okm = __ballot_sync(0xffffffffu, ok);
         const uint32_t gm = nf3_group_lane_mask<LPG>(lane);
         const bool fast = (okm & gm) == gm;
@@ -181,18 +212,7 @@ __global__ void __launch_bounds__(kNf3ThrThreads) nf3_thr_fwd_kernel(const uint8
 #pragma unroll
             for (int v = 0; v < 2; ++v)
 #pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    const h2 x2 = P::from_bits(raw[v].r[i]);
-                    uint32_t o = v2[0];
-#pragma unroll
-                    for (int k = 0; k < 7; ++k) {
-                        const h2 tk = P::from_bits(sh[k % LPG][(k / LPG) / 2]);
-                        const h2 t2 = ((k / LPG) & 1) ? P::dup_hi(tk) : P::dup_lo(tk);
-                        const uint32_t m = __hge2_mask(x2, t2);
-                        asm("lop3.b32 %0, %1, %2, %3, 0xCA;" : "=r"(o) : "r"(m), "r"(v2[k + 1]), "r"(o));   // m ? v : o
-                    }
-                    out[v].r[i] = o;
-                }
+                for (int i = 0; i < 8; ++i) out[v].r[i] = nf3_select<DT, LPG>(raw[v].r[i], sh, v2);
             if (valid) {
                 stg256(dq + idx * 64, out[0]);
                 stg256(dq + idx * 64 + 32, out[1]);
@@ -236,6 +256,186 @@ bool launch_nf3_thr_fwd(const void* w, void* dq, const void* cmin, const void* c
     } else {
         if (cmin) nf3_thr_fwd_g<kF16, true>(wp, op, cmin, cmax, nchunk, G, tab, st);
         else nf3_thr_fwd_g<kF16, false>(wp, op, cmin, cmax, nchunk, G, tab, st);
+    }
+    return true;
+}
+
+// ------------------------------------------------------------------------------------------------ STE backward
+// SteN2F3Quantizer backward: gw = gy, plus at the group's max (min) element(s)
+//   sign(max) * sum_{x >= 0} gy * (y - x / sp) / #max      (sign(min) * sum_{x < 0} gy * (y - x / sn) / #min),
+// y = the snapped level.  With the forward's x-space thresholds y is one packed select per pair, and the four group
+// sums  sum gy*y, sum_{x>=0} gy*y, sum gy*x, sum_{x>=0} gy*x  are dot products along the group: they run on the tensor
+// pipe (mma.sync m16n8k16, fp32 accumulate; products of two T values are exact in fp32) instead of 5 fp32 ops per
+// element on the FMA/ALU pipes.  Fragment trick: a warp chunk is 8 groups x 128, group i = lanes 4i..4i+3, each lane
+// owning 32 consecutive elements.  A rows 0-7 = gy of group i (rows 8-15 = gy masked to x >= 0), B column n = y (or x)
+// of group n, both taken from the lane's OWN registers: lane 4i+t supplies A[i][k-slice t] and B[k-slice t][i], so the
+// diagonal D[i][i] (D[8+i][i]) is exactly group i's dot product whatever k order the fragment layout implies.  The 56
+// off-diagonal products are wasted; the tensor pipe is otherwise idle.  Tie counts (#max, #min) the same way with
+// A = [x == max], [x == min] as 1.0 / 0.0 and B = 1.
+template <int DT>
+__device__ __forceinline__ void mma_16816(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0,
+                                          uint32_t b1) {
+    if constexpr (DT == kBF16)
+        asm("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+            : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+    else
+        asm("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+            : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+// gy pair (+ tmax where x == mx) (+ tmin where x == mn), evaluated in fp32 and rounded once
+template <int DT>
+__device__ __forceinline__ uint32_t nf3_bwd_fix(uint32_t g, uint32_t x, uint32_t mx2, uint32_t mn2, float tmax, float tmin) {
+    using P = P2<DT>;
+    float lo = P::lo(P::from_bits(g)), hi = P::hi(P::from_bits(g));
+    if constexpr (DT == kBF16)
+        asm("{ .reg .pred p, q, r, s;\n setp.eq.bf16x2 p|q, %4, %5;\n setp.eq.bf16x2 r|s, %4, %6;\n"
+            " @p add.f32 %0, %0, %2;\n @q add.f32 %1, %1, %2;\n @r add.f32 %0, %0, %3;\n @s add.f32 %1, %1, %3;\n }"
+            : "+f"(lo), "+f"(hi) : "f"(tmax), "f"(tmin), "r"(x), "r"(mx2), "r"(mn2));
+    else
+        asm("{ .reg .pred p, q, r, s;\n setp.eq.f16x2 p|q, %4, %5;\n setp.eq.f16x2 r|s, %4, %6;\n"
+            " @p add.f32 %0, %0, %2;\n @q add.f32 %1, %1, %2;\n @r add.f32 %0, %0, %3;\n @s add.f32 %1, %1, %3;\n }"
+            : "+f"(lo), "+f"(hi) : "f"(tmax), "f"(tmin), "r"(x), "r"(mx2), "r"(mn2));
+    return P::bits(P::pack(lo, hi));
+}
+
+// op-by-op path for one lane's 32 elements (its group = 4 lanes); called by the whole warp
+template <int DT>
+__device__ __noinline__ void nf3_bwd_slow_global(const void* w, const void* gy, void* gw, int64_t e0, bool valid, float mx,
+                                                 float mn, const Nf3Tables& t) {
+    const Nf3Q p = nf3_group_params(mx, mn);
+    float Gp = 0.f, Gn = 0.f;
+    int cnt = 0;
+    if (valid) {
+#pragma unroll 1
+        for (int i = 0; i < 32; ++i) {
+            const float x = load_scalar<DT>(w, e0 + i), g = load_scalar<DT>(gy, e0 + i);
+            float q, y;
+            int code;
+            nf3_elem<DT>(x, p, t, q, y, code);
+            if (x >= 0.f) Gp += g * (y - x * p.yp);
+            else Gn += g * (y - x * p.yn);
+            cnt += (x == mx ? 1 : 0) + (x == mn ? 65536 : 0);
+        }
+    }
+    Gp = group_sum<4>(Gp);
+    Gn = group_sum<4>(Gn);
+    cnt = group_sum_i<4>(cnt);
+    const float sgx = mx > 0.f ? 1.f : (mx < 0.f ? -1.f : 0.f);
+    const float sgn = mn > 0.f ? 1.f : (mn < 0.f ? -1.f : 0.f);
+    const float tmax = sgx * Gp / (float)(cnt & 0xffff), tmin = sgn * Gn / (float)(cnt >> 16);
+    if (valid) {
+#pragma unroll 1
+        for (int i = 0; i < 32; ++i) {
+            const float x = load_scalar<DT>(w, e0 + i);
+            float r = load_scalar<DT>(gy, e0 + i);
+            if (x == mx) r += tmax;
+            if (x == mn) r += tmin;
+            if (p.nan_group) r = __int_as_float(0x7fc00000);
+            store_scalar<DT>(gw, e0 + i, r);
+        }
+    }
+}
+
+template <int DT>
+__global__ void __launch_bounds__(kNf3ThrThreads) nf3_thr_bwd_kernel(const uint8_t* __restrict__ w, const uint8_t* __restrict__ gy,
+                                                                     uint8_t* __restrict__ gw, int64_t nchunk,
+                                                                     const __grid_constant__ Nf3Tables tab,
+                                                                     const __grid_constant__ Nf3Stair st) {
+    using P = P2<DT>;
+    using h2 = typename P::h2;
+    constexpr int LPG = 4, R = 2, NP = 1;
+    const int lane = threadIdx.x & 31;
+    const int lig = lane & 3, gbase = lane & ~3, grp = lane >> 2;
+    const int64_t warp = (int64_t)blockIdx.x * (kNf3ThrThreads / 32) + (threadIdx.x >> 5);
+    const int64_t nwarps = (int64_t)gridDim.x * (kNf3ThrThreads / 32);
+    const int64_t nwc = (nchunk + 31) / 32;
+    const uint32_t ones = (DT == kBF16) ? 0x3f803f80u : 0x3c003c00u;
+    Nf3Step my[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) my[r] = st.k[lig + r * LPG];
+    for (int64_t wc = warp; wc < nwc; wc += nwarps) {
+        const int64_t idx = wc * 32 + lane;
+        const bool valid = idx < nchunk;
+        U8 rx[2], rg[2];
+        if (valid) {
+            rx[0] = ldg256(w + idx * 64);
+            rx[1] = ldg256(w + idx * 64 + 32);
+            rg[0] = ldg256(gy + idx * 64);
+            rg[1] = ldg256(gy + idx * 64 + 32);
+        } else {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) rx[0].r[i] = rx[1].r[i] = rg[0].r[i] = rg[1].r[i] = 0;
+        }
+        float mx, mn, mx1, mn1;
+        vec_minmax16<DT>(rx[0], mx, mn);
+        vec_minmax16<DT>(rx[1], mx1, mn1);
+        mx = group_max<LPG>(fmaxf(mx, mx1));
+        mn = group_min<LPG>(fminf(mn, mn1));
+        const float sp = fabsf(mx), sn = fabsf(mn);
+        uint32_t sh[LPG][NP];
+        bool ok = nf3_group_thresholds<DT, LPG>(my, st.mask, sp, sn, lig, gbase, sh);
+        ok = ok && (mx > 0.f) && (mn < 0.f);
+        if (__all_sync(0xffffffffu, ok || !valid)) {
+            uint32_t lv[8];
+#pragma unroll
+            for (int c = 0; c < 8; ++c) lv[c] = st.lvl2[c];
+            const uint32_t mx2 = P::bits(P::dup(mx)), mn2 = P::bits(P::dup(mn));
+            const h2 zero2 = P::from_bits(0u);
+            float dy[4] = {0.f, 0.f, 0.f, 0.f}, dx[4] = {0.f, 0.f, 0.f, 0.f}, dc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+            for (int v = 0; v < 2; ++v)
+#pragma unroll
+                for (int i = 0; i < 8; i += 2) {
+                    const uint32_t x0 = rx[v].r[i], x1 = rx[v].r[i + 1], g0 = rg[v].r[i], g1 = rg[v].r[i + 1];
+                    const uint32_t y0 = nf3_select<DT, LPG>(x0, sh, lv), y1 = nf3_select<DT, LPG>(x1, sh, lv);
+                    const uint32_t p0 = g0 & __hge2_mask(P::from_bits(x0), zero2), p1 = g1 & __hge2_mask(P::from_bits(x1), zero2);
+                    mma_16816<DT>(dy, g0, p0, g1, p1, y0, y1);
+                    mma_16816<DT>(dx, g0, p0, g1, p1, x0, x1);
+                    const uint32_t e0 = P::bits(__heq2(P::from_bits(x0), P::from_bits(mx2)));
+                    const uint32_t e1 = P::bits(__heq2(P::from_bits(x1), P::from_bits(mx2)));
+                    const uint32_t f0 = P::bits(__heq2(P::from_bits(x0), P::from_bits(mn2)));
+                    const uint32_t f1 = P::bits(__heq2(P::from_bits(x1), P::from_bits(mn2)));
+                    mma_16816<DT>(dc, e0, f0, e1, f1, ones, ones);
+                }
+            // D[i][i] sits in lane 4i + (i >> 1), register i & 1 (rows 0-7) / 2 + (i & 1) (rows 8-15)
+            const int src = gbase + (grp >> 1);
+            const bool odd = grp & 1;
+            const float sy_all = __shfl_sync(0xffffffffu, odd ? dy[1] : dy[0], src);
+            const float sy_pos = __shfl_sync(0xffffffffu, odd ? dy[3] : dy[2], src);
+            const float sx_all = __shfl_sync(0xffffffffu, odd ? dx[1] : dx[0], src);
+            const float sx_pos = __shfl_sync(0xffffffffu, odd ? dx[3] : dx[2], src);
+            // every column of the count product equals the group's count: no exchange
+            const float tmax = __fdividef(sy_pos - __fdividef(sx_pos, sp), dc[0]);
+            const float tmin = -__fdividef((sy_all - sy_pos) - __fdividef(sx_all - sx_pos, sn), dc[2]);
+            U8 out[2];
+#pragma unroll
+            for (int v = 0; v < 2; ++v)
+#pragma unroll
+                for (int i = 0; i < 8; ++i) out[v].r[i] = nf3_bwd_fix<DT>(rg[v].r[i], rx[v].r[i], mx2, mn2, tmax, tmin);
+            if (valid) {
+                stg256(gw + idx * 64, out[0]);
+                stg256(gw + idx * 64 + 32, out[1]);
+            }
+        } else {
+            nf3_bwd_slow_global<DT>(w, gy, gw, idx * 32, valid, mx, mn, tab);
+        }
+    }
+}
+
+// Returns true if the threshold backward was launched (16-bit dtype, group 128, 32-byte aligned).
+bool launch_nf3_thr_bwd(const void* w, const void* gy, void* gw, int64_t n, int G, int dtype, int sem, cudaStream_t st) {
+    if ((dtype != kBF16 && dtype != kF16) || G != 128) return false;
+    if (((uintptr_t)w % 32) || ((uintptr_t)gy % 32) || ((uintptr_t)gw % 32) || (n % 128)) return false;
+    const Nf3Tables tab = make_tables(dtype, sem);
+    const int64_t nchunk = n / 32;
+    const int grid = nf3_thr_grid(nchunk);
+    if (dtype == kBF16) {
+        nf3_thr_bwd_kernel<kBF16><<<grid, kNf3ThrThreads, 0, st>>>((const uint8_t*)w, (const uint8_t*)gy, (uint8_t*)gw, nchunk,
+                                                                    tab, make_stair(tab, kBF16));
+    } else {
+        nf3_thr_bwd_kernel<kF16><<<grid, kNf3ThrThreads, 0, st>>>((const uint8_t*)w, (const uint8_t*)gy, (uint8_t*)gw, nchunk, tab,
+                                                                   make_stair(tab, kF16));
     }
     return true;
 }
