@@ -317,8 +317,15 @@ def secondary_metrics(torch, dev, peak):
     """BASELINE configs[3] and configs[4] at N=1: seconds for the int2-g128 clip search over all Llama-2-7B linears
     (tools/bench_multi.py) and tok/s of the Qwen3-8B packed int2 decode GEMV chain (tools/bench_gemv.py: CUDA graph +
     PDL, 4 fused launches per layer, dependent inputs, 1.859 GB of packed weights per token = L2-cold)."""
-    from tools import bench_gemv, bench_multi
+    from tools import bench_gemv, bench_multi, bench_nf3
     out = {}
+    nf = {r["kernel"]: r for r in bench_nf3.run(dev, peak)}
+    out["nf3_g128_llama2_7b_layer"] = {
+        "what": "configs[2]: one decoder layer's flat bf16 buffer (202.4 M weights) per launch, 3 rotating buffers",
+        "fwd_with_clip_cache_gbs": nf["nf3 fwd + clip (config 3)"]["gbs"],
+        "fwd_with_clip_cache_frac_of_hbm_peak": nf["nf3 fwd + clip (config 3)"]["frac_of_hbm_peak"],
+        "fwd_gbs": nf["nf3 fwd"]["gbs"], "fwd_frac_of_hbm_peak": nf["nf3 fwd"]["frac_of_hbm_peak"],
+        "ste_bwd_gbs": nf["nf3 ste bwd"]["gbs"], "ste_bwd_frac_of_hbm_peak": nf["nf3 ste bwd"]["frac_of_hbm_peak"]}
     ac = bench_multi.bench_autoclip(dev, 0, 1)
     out["autoclip_7b_int2_g128"] = {"seconds": ac["seconds_total"], "n_gpus": 1, "pairs": ac["pairs"], "candidates": 100,
                                     "tokens": 512}

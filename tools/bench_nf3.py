@@ -9,13 +9,13 @@ import torch
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from bitdistiller_b200 import _lib as L  # noqa: E402
-from microbench import timeit  # noqa: E402
+try:
+    from microbench import timeit  # noqa: E402
+except ImportError:
+    from tools.microbench import timeit  # noqa: E402
 
 
-def main():
-    dev = torch.device("cuda:0")
-    peak = json.load(open(os.path.join(os.path.dirname(__file__), "..", "MEASURED_PEAKS.json"))).get("hbm_gbs", 6553.3) \
-        if os.path.exists(os.path.join(os.path.dirname(__file__), "..", "MEASURED_PEAKS.json")) else 6553.3
+def run(dev, peak):
     N = 4 * 4096 * 4096 + 3 * 11008 * 4096
     nbuf = 3
     ws = [(torch.randn(N, device=dev) * 0.02).to(torch.bfloat16) for _ in range(nbuf)]
@@ -38,11 +38,23 @@ def main():
     def ifwd(i):
         lib.bdq_int_fakequant_fwd(L.ptr(ws[i]), L.ptr(out), None, None, None, None, None, n, 128, 2, 1, 1, 0, st)
 
+    res = []
     for name, fn, bpw in [("int2 fwd", ifwd, 4), ("nf3 fwd", nfwd, 4), ("nf3 fwd + clip (config 3)", nclip, 4 + 4 / 128),
                           ("nf3 ste bwd", nbwd, 6)]:
         t = timeit(fn, nbuf)
         gbs = N * bpw / t / 1e9
-        print(f"bf16 flat layer {name:28s} {t*1e6:8.1f} us  {gbs:7.1f} GB/s  {gbs/peak*100:5.1f}% of HBM peak ({peak:.0f})")
+        res.append({"kernel": name, "us_per_layer": t * 1e6, "gbs": gbs, "frac_of_hbm_peak": gbs / peak,
+                    "bytes_per_weight": bpw, "weights": N})
+    return res
+
+
+def main():
+    dev = torch.device("cuda:0")
+    pk = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "MEASURED_PEAKS.json")
+    peak = json.load(open(pk)).get("hbm_gbs", 6553.3) if os.path.exists(pk) else 6553.3
+    for r in run(dev, peak):
+        print(f"bf16 flat layer {r['kernel']:28s} {r['us_per_layer']:8.1f} us  {r['gbs']:7.1f} GB/s  "
+              f"{r['frac_of_hbm_peak']*100:5.1f}% of HBM peak ({peak:.0f})")
 
 
 if __name__ == "__main__":
