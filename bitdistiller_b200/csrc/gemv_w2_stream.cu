@@ -126,12 +126,12 @@ __host__ __device__ inline int gemv_t_meta_bytes(int zw) { return 16 * zw * 32 +
 // [kRedSlots] meta slots | red | barriers
 __host__ __device__ inline int gemv_t_smem_bytes(int wpw, int zw, int depth) {
     return 1024 + kSWarps * depth * kItemBytes + kSWarps * (wpw * kWinStride + kZeroBytes) + kRedSlots * gemv_t_meta_bytes(zw) +
-           kRedSlots * kSWarps * 16 * 4 + (kSWarps * 8 + kRedSlots) * 8;
+           kRedSlots * kSWarps * 64 * 4 + (kSWarps * 8 + kRedSlots) * 8;
 }
 
 // shared memory per warp: its windows of x (extraction order) + the zero block
 __host__ __device__ inline int gemv_s_warp_bytes(int wpw) { return wpw * kWinStride + kZeroBytes; }
-__host__ __device__ inline int gemv_s_smem_bytes(int wpw) { return kSWarps * gemv_s_warp_bytes(wpw) + kRedSlots * kSWarps * 16 * 4; }
+__host__ __device__ inline int gemv_s_smem_bytes(int wpw) { return kSWarps * gemv_s_warp_bytes(wpw) + kRedSlots * kSWarps * 64 * 4; }
 
 __device__ __forceinline__ unsigned long long gtime() {
     unsigned long long v;
@@ -203,10 +203,10 @@ __global__ void __launch_bounds__(kSThreads, 2) gemv_w2s_kernel(const __half* __
     const int mywin = warp < nwin ? (nwin - warp + kSWarps - 1) / kSWarps : 0;   // windows warp, warp+8, ...
     uint8_t* wbase = smem + (size_t)warp * gemv_s_warp_bytes(wpw);
     uint8_t* zblock = wbase + (size_t)wpw * kWinStride;
-    float* red = reinterpret_cast<float*>(smem + (size_t)kSWarps * gemv_s_warp_bytes(wpw));   // [kRedSlots][8][16]
+    float* red = reinterpret_cast<float*>(smem + (size_t)kSWarps * gemv_s_warp_bytes(wpw));   // [kRedSlots][8 warps][4 quad lanes][16]
     // TMA variant: meta slots (scales + zero words of one 16-channel block each) and the mbarriers
     const int meta_bytes = gemv_t_meta_bytes(zw);
-    uint8_t* meta = reinterpret_cast<uint8_t*>(red) + kRedSlots * kSWarps * 16 * 4;
+    uint8_t* meta = reinterpret_cast<uint8_t*>(red) + kRedSlots * kSWarps * 64 * 4;
     uint64_t* wbar = reinterpret_cast<uint64_t*>(meta + kRedSlots * meta_bytes) + warp * 8;   // this warp's item barriers
     uint64_t* mbar = reinterpret_cast<uint64_t*>(meta + kRedSlots * meta_bytes) + kSWarps * 8;   // [kRedSlots]
     uint8_t* wring = ring + (size_t)warp * depth * kItemBytes;
@@ -250,31 +250,47 @@ __global__ void __launch_bounds__(kSThreads, 2) gemv_w2s_kernel(const __half* __
             for (int d = 0; d < depth; ++d) issue_tma();
     }
 
-    // ---- producer cursor: item = (16-channel block, window of this warp)
+    // ---- producer cursor: item = (16-channel block, window of this warp).  The three row pointers of the current block
+    // (this lane's row g, first window) are kept and stepped; only a change of matrix recomputes them.
     int p_rb = rb0, p_j = 0, p_mi = mat_of(rb0);
+    const int G0 = 4 * warp + t;
+    const uint8_t* pa0 = nullptr;
+    const __half* ps0 = nullptr;
+    const uint32_t* pz0 = nullptr;
+    auto set_base = [&]() {
+        const size_t r = (size_t)(p_rb - rstart_of(p_mi)) * 16 + g;
+        pa0 = qw_of(p_mi) + r * row_bytes + (size_t)G0 * 32;
+        ps0 = sc_of(p_mi) + r * zw16 + G0;   // G < zw16 always (scales are zero-padded to zw16 columns)
+        pz0 = qz_of(p_mi) + r * zw + (G0 >> 4);
+    };
+    if constexpr (!TMA) { if (rb0 < rb1) set_base(); }
     auto issue = [&](ItemBuf& b) {
         if (p_rb >= rb1) return;
-        const size_t r = (size_t)(p_rb - rstart_of(p_mi)) * 16 + g;
-        const int win = warp + kSWarps * p_j;
-        const int G = 4 * win + t;
-        if (G < ngrp) {
-            const uint8_t* pa = qw_of(p_mi) + r * row_bytes + (size_t)G * 32;
+        if (G0 + 32 * p_j < ngrp) {
+            const uint8_t* pa = pa0 + p_j * 1024;
             b.a = ldg256(pa);
             b.b = ldg256(pa + (size_t)8 * row_bytes);
         } else {
 #pragma unroll
             for (int i = 0; i < 8; ++i) b.a.r[i] = b.b.r[i] = 0u;
         }
-        const __half* ps = sc_of(p_mi) + r * zw16 + G;   // G < zw16 always (scales are zero-padded to zw16 columns)
+        const __half* ps = ps0 + 32 * p_j;
         b.sa = ldg_nc_u16(ps);
         b.sb = ldg_nc_u16(ps + (size_t)8 * zw16);
-        const uint32_t* pz = qz_of(p_mi) + r * zw + (G >> 4);
+        const uint32_t* pz = pz0 + 2 * p_j;
         b.za = ldg_nc_u32(pz);
         b.zb = ldg_nc_u32(pz + (size_t)8 * zw);
         if (++p_j == mywin) {
             p_j = 0;
             ++p_rb;
-            p_mi = mat_of(p_rb);
+            if (p_rb >= m.rb_end[p_mi]) {
+                p_mi = mat_of(p_rb);
+                if (p_rb < rb1) set_base();
+            } else {
+                pa0 += (size_t)16 * row_bytes;
+                ps0 += (size_t)16 * zw16;
+                pz0 += (size_t)16 * zw;
+            }
         }
     };
     ItemBuf buf[TMA ? 1 : kDepth];
@@ -358,14 +374,20 @@ __global__ void __launch_bounds__(kSThreads, 2) gemv_w2s_kernel(const __half* __
                 hi[i] = __byte_perm(p01, p23, 0x7632);
             }
             uint8_t* wj = wbase + (size_t)(j0 + jj) * kWinStride;
-            const int grp = lane >> 3, w = lane & 7;   // slot = 2*grp + limb; inside: [pair w>>1][w&1][i][j]
-            uint8_t* dst = wj + (2 * grp) * kSlotStride + (w >> 1) * 32 + (w & 1) * 16;
-            *reinterpret_cast<uint4*>(dst) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-            *reinterpret_cast<uint4*>(dst + kSlotStride) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+            const int grp = lane >> 3, w = lane & 7;   // slot = 2*grp + limb; inside: [pair w>>1][digit i][w&1][j]:
+            // the B operand of digit i (words 2p, 2p+1) is one aligned 8-byte pair of the consumer's LDS.128
+            uint8_t* dst = wj + (2 * grp) * kSlotStride + (w >> 1) * 32 + (w & 1) * 4;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                *reinterpret_cast<uint32_t*>(dst + i * 8) = hi[i];
+                *reinterpret_cast<uint32_t*>(dst + kSlotStride + i * 8) = lo[i];
+            }
 #pragma unroll
             for (int sft = 1; sft < 8; sft <<= 1) qsum += __shfl_xor_sync(0xffffffffu, qsum, sft);
             // 128 elements x 0x4B400080 = 0xA0004000 (mod 2^32)
-            if (w == 0) reinterpret_cast<float2*>(wj + kMetaOff)[grp] = make_float2(unit, (float)(int)(qsum - 0xA0004000u));
+            // meta: (unit / 64, 64 * sum q): the digit planes are combined as integers scaled by 64 (consume)
+            if (w == 0)
+                reinterpret_cast<float2*>(wj + kMetaOff)[grp] = make_float2(unit * 0.015625f, __int_as_float((int)(qsum - 0xA0004000u) * 64));
         }
     }
     __syncwarp();
@@ -386,10 +408,10 @@ __global__ void __launch_bounds__(kSThreads, 2) gemv_w2s_kernel(const __half* __
         __syncthreads();
         if (tid < rslot * 16) {
             const int sl = tid >> 4, row = tid & 15;
-            const float* rp = red + sl * kSWarps * 16 + row;
+            const float* rp = red + sl * kSWarps * 64 + row;
             float acc = 0.f;
 #pragma unroll
-            for (int w = 0; w < kSWarps; ++w) acc += rp[w * 16];
+            for (int w = 0; w < kSWarps * 4; ++w) acc += rp[w * 16];
             const int rb = rb_base + sl;
             const int mi = mat_of(rb);
             const int rstart = rstart_of(mi);
@@ -407,15 +429,9 @@ __global__ void __launch_bounds__(kSThreads, 2) gemv_w2s_kernel(const __half* __
         if (rb_base < rb1) __syncthreads();   // the slots are written again
     };
     auto flush = [&]() {
-        fin_lo += __shfl_xor_sync(0xffffffffu, fin_lo, 1);
-        fin_hi += __shfl_xor_sync(0xffffffffu, fin_hi, 1);
-        fin_lo += __shfl_xor_sync(0xffffffffu, fin_lo, 2);
-        fin_hi += __shfl_xor_sync(0xffffffffu, fin_hi, 2);
-        float* my = red + (rslot * kSWarps + warp) * 16;
-        if (t == 0) {
-            my[g] = fin_lo;
-            my[g + 8] = fin_hi;
-        }
+        float* my = red + ((rslot * kSWarps + warp) * 4 + t) * 16;   // the quad's 4 partials are summed in block_reduce
+        my[g] = fin_lo;
+        my[g + 8] = fin_hi;
         fin_lo = fin_hi = 0.f;
         if (++rslot == kRedSlots) block_reduce();
     };
@@ -435,26 +451,29 @@ __global__ void __launch_bounds__(kSThreads, 2) gemv_w2s_kernel(const __half* __
         for (int i = 0; i < 4; ++i) acc[i][0] = acc[i][1] = acc[i][2] = acc[i][3] = 0;
 #pragma unroll
         for (int p2 = 0; p2 < 4; ++p2) {   // word pair (2 p2, 2 p2 + 1) of the group = 32 codes of each digit
-            const uint4 q0 = *reinterpret_cast<const uint4*>(bp + p2 * 32);        // x limbs for word 2 p2, digits 0..3
-            const uint4 q1 = *reinterpret_cast<const uint4*>(bp + p2 * 32 + 16);   // word 2 p2 + 1
+            const uint4 q0 = *reinterpret_cast<const uint4*>(bp + p2 * 32);        // x limbs: digit 0 (2 words), digit 1
+            const uint4 q1 = *reinterpret_cast<const uint4*>(bp + p2 * 32 + 16);   // digit 2, digit 3
             const uint32_t a0 = b.a.r[2 * p2], a1 = b.b.r[2 * p2], a2 = b.a.r[2 * p2 + 1], a3 = b.b.r[2 * p2 + 1];
-            imma16832(acc[0], a0 & 0x03030303u, a1 & 0x03030303u, a2 & 0x03030303u, a3 & 0x03030303u, q0.x, q1.x);
-            imma16832(acc[1], a0 & 0x0C0C0C0Cu, a1 & 0x0C0C0C0Cu, a2 & 0x0C0C0C0Cu, a3 & 0x0C0C0C0Cu, q0.y, q1.y);
-            imma16832(acc[2], a0 & 0x30303030u, a1 & 0x30303030u, a2 & 0x30303030u, a3 & 0x30303030u, q0.z, q1.z);
-            imma16832(acc[3], a0 & 0xC0C0C0C0u, a1 & 0xC0C0C0C0u, a2 & 0xC0C0C0C0u, a3 & 0xC0C0C0C0u, q0.w, q1.w);
+            imma16832(acc[0], a0 & 0x03030303u, a1 & 0x03030303u, a2 & 0x03030303u, a3 & 0x03030303u, q0.x, q0.y);
+            imma16832(acc[1], a0 & 0x0C0C0C0Cu, a1 & 0x0C0C0C0Cu, a2 & 0x0C0C0C0Cu, a3 & 0x0C0C0C0Cu, q0.z, q0.w);
+            imma16832(acc[2], a0 & 0x30303030u, a1 & 0x30303030u, a2 & 0x30303030u, a3 & 0x30303030u, q1.x, q1.y);
+            imma16832(acc[3], a0 & 0xC0C0C0C0u, a1 & 0xC0C0C0C0u, a2 & 0xC0C0C0C0u, a3 & 0xC0C0C0C0u, q1.z, q1.w);
         }
-        // this lane's columns 2t, 2t+1 = (hi, lo) limb sums of group t: rows g (acc[.][0..1]) and g+8 (acc[.][2..3])
-        const float2 mt = *reinterpret_cast<const float2*>(wbase + (size_t)c_j * kWinStride + kMetaOff + t * 8);   // (unit, sum q)
+        // this lane's columns 2t, 2t+1 = (hi, lo) limb sums of group t: rows g (acc[.][0..1]) and g+8 (acc[.][2..3]).
+        // Plane i carries 4^i: u = 64 a0 + 16 a1 + 4 a2 + a3 = 64 * sum code * limb (|u| < 2^24), then
+        // 256 u_hi + u_lo - z * 64 sum q = 64 * sum (code - z) * q  (< 2^28: int32 exact, one rounding in the I2F).
+        const float2 mt = *reinterpret_cast<const float2*>(wbase + (size_t)c_j * kWinStride + kMetaOff + t * 8);   // (unit/64, 64 sum q)
+        const int sq64 = __float_as_int(mt.y);
         const int sh = ((4 * (warp + kSWarps * c_j) + t) & 15) * 2;
-        const float za = (float)((b.za >> sh) & 3u), zb = (float)((b.zb >> sh) & 3u);
+        const int za = (int)((b.za >> sh) & 3u), zb = (int)((b.zb >> sh) & 3u);
+        int u[4];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) u[c] = ((acc[0][c] * 4 + acc[1][c]) * 4 + acc[2][c]) * 4 + acc[3][c];
+        const int wa = u[0] * 256 + u[1] - za * sq64, wb = u[2] * 256 + u[3] - zb * sq64;
         const float sa = __half2float(__ushort_as_half((unsigned short)b.sa)) * mt.x;
         const float sb = __half2float(__ushort_as_half((unsigned short)b.sb)) * mt.x;
-        float v[4];
-#pragma unroll
-        for (int c = 0; c < 4; ++c)
-            v[c] = fmaf((float)acc[3][c], 0.015625f, fmaf((float)acc[2][c], 0.0625f, fmaf((float)acc[1][c], 0.25f, (float)acc[0][c])));
-        fin_lo = fmaf(sa, fmaf(256.f, v[0], v[1]) - za * mt.y, fin_lo);
-        fin_hi = fmaf(sb, fmaf(256.f, v[2], v[3]) - zb * mt.y, fin_hi);
+        fin_lo = fmaf(sa, (float)wa, fin_lo);
+        fin_hi = fmaf(sb, (float)wb, fin_hi);
     };
 
     const int nitems = (rb1 - rb0) * mywin;
