@@ -13,7 +13,7 @@ def _check_fp16(*ts):
             raise TypeError(f"expected a float16 tensor (the reference kernels are fp16-only), got {t.dtype}")
 
 
-GEMV_PDL, GEMV_CTAS1, GEMV_RING = 1, 2, 4   # include/bdq.h
+GEMV_PDL, GEMV_CTAS1, GEMV_RING, GEMV_SILU_MUL = 1, 2, 4, 64   # include/bdq.h
 
 
 def gemv_forward_cuda(in_feats, kernel, scaling_factors, zeros, w_bit, group_size, pdl=False, flags=0):
@@ -67,6 +67,35 @@ def gemv_multi_forward_cuda(in_feats, kernels, scaling_factors, zeros, group_siz
                                        npf, pf_ptr, pf_len, L.stream_ptr(x.device))
     L.check(rc, "bdq_gemv_w2_multi")
     return outs
+
+
+def gemv_silu_mul_forward_cuda(in_feats, gate, up, group_size, pdl=False, flags=0, out=None):
+    """Batch-1 fused MLP front half (inference/modules/fused_mlp.py:44-108, rows == 1): silu(x @ gate^T) * (x @ up^T) in
+    ONE launch.  `gate` / `up` = (qweight, scales, qzeros) of two packed matrices with equal out_features; the kernel
+    walks their 16-channel blocks interleaved and applies the reference's three fp16 roundings (after the GEMV, after
+    F.silu, after the product) in the split-K epilogue.  Returns [1, OC] fp16."""
+    import ctypes
+    L.require_cuda(in_feats, *gate, *up)
+    _check_fp16(in_feats, gate[1], up[1])
+    x = in_feats.contiguous()
+    if x.numel() != x.shape[-1]:
+        raise ValueError("gemv_silu_mul_forward_cuda is the batch-1 decode path: in_feats must hold one row")
+    IC, OC = x.shape[-1], gate[0].shape[0]
+    if up[0].shape[0] != OC:
+        raise ValueError("gate and up must have the same out_features")
+    for k, s, z in (gate, up):
+        assert k.is_contiguous() and s.is_contiguous() and z.is_contiguous() and k.shape[1] * 16 == IC
+    if out is None:
+        out = torch.empty((1, OC), dtype=torch.float16, device=x.device)
+    arr = lambda a, b: (ctypes.c_void_p * 2)(a.data_ptr(), b.data_ptr())
+    outs = (ctypes.c_void_p * 2)(out.data_ptr(), None)
+    oc = (ctypes.c_int64 * 2)(OC, OC)
+    with torch.cuda.device(x.device):
+        rc = L.lib().bdq_gemv_w2_multi(L.ptr(x), 2, arr(gate[0], up[0]), arr(gate[1], up[1]), arr(gate[2], up[2]), outs, oc,
+                                       L.i64(IC), int(group_size), int(flags) | GEMV_SILU_MUL | (GEMV_PDL if pdl else 0),
+                                       0, None, None, L.stream_ptr(x.device))
+    L.check(rc, "bdq_gemv_w2_multi(silu_mul)")
+    return out
 
 
 def gemm_forward_cuda(in_feats, kernel, scaling_factors, zeros, group_size, split_k_iters, w_bit=2):

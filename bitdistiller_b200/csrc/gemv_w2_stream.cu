@@ -60,6 +60,7 @@ struct GemvMats {
     unsigned long long pf_bytes[kMaxMats];
     __half* peer[kMaxMats][kMaxPeers];  // tensor parallel: the same channel slice inside every peer GPU's output row
     int npeer;
+    int silu;   // 1: two matrices (gate, up) walked as interleaved 16-channel blocks, out[0] = silu(gate) * up
 };
 
 struct GemvMaps {   // TMA variant: one 2-D tensor map per matrix, [OC rows][IC/4 bytes] uint8, box 16 rows x 128 B, SWIZZLE_128B
@@ -158,7 +159,8 @@ __global__ void __launch_bounds__(kSThreads, 2) gemv_w2s_kernel(const __half* __
     auto mark = [&]() {
         if constexpr (PROF) {
             if ((threadIdx.x & 31) == 0 && pslot < 16)
-                prof[((size_t)blockIdx.x * kSWarps + (threadIdx.x >> 5)) * 16 + pslot] = gtime();
+                prof[((size_t)blockIdx.x * kSWarps + (threadIdx.x >> 5)) * 16 + pslot] =
+                    (gtime() & 0xffffffffffull) | ((unsigned long long)clock64() << 40);   // 40 bits of ns | 24 bits of SM cycles
             ++pslot;
         }
     };
@@ -169,14 +171,17 @@ __global__ void __launch_bounds__(kSThreads, 2) gemv_w2s_kernel(const __half* __
     const int ngrp = IC >> 7, nwin = (ngrp + 3) >> 2;
     const int row_bytes = IC >> 2, zw16 = zw * 16;
     // balanced contiguous split of the 16-channel blocks: the first (total_rb % grid) CTAs take one more (no division here)
-    const int rb0 = (int)blockIdx.x * rb_q + min((int)blockIdx.x, rb_r);
-    const int rb1 = rb0 + rb_q + ((int)blockIdx.x < rb_r ? 1 : 0);
+    // (gate/up mode: the unit is a pair of blocks, so every CTA starts on a gate block)
+    const int rb_u = m.silu ? 2 : 1;
+    const int rb0 = ((int)blockIdx.x * rb_q + min((int)blockIdx.x, rb_r)) * rb_u;
+    const int rb1 = rb0 + (rb_q + ((int)blockIdx.x < rb_r ? 1 : 0)) * rb_u;
     // matrix lookup without dynamically indexed constant loads (those are dependent long-latency LDCs in the prologue)
     // (the TMA variant has registers to spare and keeps everything in registers; the register-streaming variant is at
     // its 128-register budget and indexes the parameter arrays instead)
     int e0 = 0, e1 = 0, e2 = 0;
     if constexpr (TMA) { e0 = m.rb_end[0]; e1 = m.rb_end[1]; e2 = m.rb_end[2]; }
     auto mat_of = [&](int rb) {   // rb_end is non-decreasing
+        if (m.silu) return rb & 1;
         if constexpr (TMA) {
             return (rb >= e0 ? 1 : 0) + (rb >= e1 ? 1 : 0) + (rb >= e2 ? 1 : 0);
         } else {
@@ -189,6 +194,7 @@ __global__ void __launch_bounds__(kSThreads, 2) gemv_w2s_kernel(const __half* __
         if constexpr (TMA) return mi == 0 ? 0 : (mi == 1 ? e0 : (mi == 2 ? e1 : e2));
         else return mi ? m.rb_end[mi - 1] : 0;
     };
+    auto blk_of = [&](int rb, int mi) { return m.silu ? (rb >> 1) : rb - rstart_of(mi); };   // block index inside its matrix
     const uint8_t *qw0 = nullptr, *qw1 = nullptr, *qw2 = nullptr, *qw3 = nullptr;
     const __half *sc0 = nullptr, *sc1 = nullptr, *sc2 = nullptr, *sc3 = nullptr;
     const uint32_t *qz0 = nullptr, *qz1 = nullptr, *qz2 = nullptr, *qz3 = nullptr;
@@ -212,7 +218,7 @@ __global__ void __launch_bounds__(kSThreads, 2) gemv_w2s_kernel(const __half* __
     uint8_t* wring = ring + (size_t)warp * depth * kItemBytes;
     auto locate = [&](int rb, int& mi, int& r0) {   // 16-channel block -> (matrix, first channel)
         mi = mat_of(rb);
-        r0 = (rb - rstart_of(mi)) * 16;
+        r0 = blk_of(rb, mi) * 16;
     };
     auto issue_meta = [&](int rb, int slot) {   // one thread: scales + zero words of block rb -> meta slot
         int mi, r0;
@@ -258,7 +264,7 @@ __global__ void __launch_bounds__(kSThreads, 2) gemv_w2s_kernel(const __half* __
     const __half* ps0 = nullptr;
     const uint32_t* pz0 = nullptr;
     auto set_base = [&]() {
-        const size_t r = (size_t)(p_rb - rstart_of(p_mi)) * 16 + g;
+        const size_t r = (size_t)blk_of(p_rb, p_mi) * 16 + g;
         pa0 = qw_of(p_mi) + r * row_bytes + (size_t)G0 * 32;
         ps0 = sc_of(p_mi) + r * zw16 + G0;   // G < zw16 always (scales are zero-padded to zw16 columns)
         pz0 = qz_of(p_mi) + r * zw + (G0 >> 4);
@@ -283,7 +289,7 @@ __global__ void __launch_bounds__(kSThreads, 2) gemv_w2s_kernel(const __half* __
         if (++p_j == mywin) {
             p_j = 0;
             ++p_rb;
-            if (p_rb >= m.rb_end[p_mi]) {
+            if (m.silu || p_rb >= m.rb_end[p_mi]) {
                 p_mi = mat_of(p_rb);
                 if (p_rb < rb1) set_base();
             } else {
@@ -414,11 +420,21 @@ __global__ void __launch_bounds__(kSThreads, 2) gemv_w2s_kernel(const __half* __
             for (int w = 0; w < kSWarps * 4; ++w) acc += rp[w * 16];
             const int rb = rb_base + sl;
             const int mi = mat_of(rb);
-            const int rstart = rstart_of(mi);
-            const __half hv = __float2half_rn(acc);
-            const size_t oi = (size_t)(rb - rstart) * 16 + row;
-            m.out[mi][oi] = hv;
-            for (int pr = 0; pr < m.npeer; ++pr) m.peer[mi][pr][oi] = hv;   // NVLink peer stores (all-gather fused in the epilogue)
+            __half hv = __float2half_rn(acc);
+            bool store = true;
+            if (m.silu) {   // slots 2i / 2i+1 = gate / up block i: lanes 0-15 / 16-31 of one warp
+                const float up = __shfl_down_sync(0xffffffffu, __half2float(hv), 16);
+                // the reference rounds to fp16 after the GEMV, after F.silu and after the product (fused_mlp.py:49-108)
+                const float gt = __half2float(hv);
+                const float sg = __half2float(__float2half_rn(gt / (1.f + __expf(-gt))));
+                hv = __float2half_rn(sg * up);
+                store = (sl & 1) == 0;
+            }
+            const size_t oi = (size_t)blk_of(rb, mi) * 16 + row;
+            if (store) {
+                m.out[mi][oi] = hv;
+                for (int pr = 0; pr < m.npeer; ++pr) m.peer[mi][pr][oi] = hv;   // NVLink peer stores (all-gather fused in the epilogue)
+            }
         }
         rb_base += rslot;
         rslot = 0;
@@ -581,12 +597,13 @@ int bdq_gemv_w2_stream_launch(const void* x, int nmat, const int32_t* const* qwe
             if (!peer_out[i * n_peer + pr]) return BDQ_ERR_UNSUPPORTED;
             m.peer[i][pr] = (__half*)peer_out[i * n_peer + pr];
         }
+    const bool silu = (flags & BDQ_GEMV_SILU_MUL) != 0;
     int total_rb = 0;
     for (int i = 0; i < kMaxMats; ++i) {
         const int k = i < nmat ? i : nmat - 1;
         if (i < nmat) {
             if (OC[i] <= 0 || OC[i] % 16 != 0 || OC[i] > (1 << 24)) return BDQ_ERR_UNSUPPORTED;
-            if (((uintptr_t)qweight[i] % 32) || ((uintptr_t)scales[i] % 4) || ((uintptr_t)qzeros[i] % 4) || !out[i])
+            if (((uintptr_t)qweight[i] % 32) || ((uintptr_t)scales[i] % 4) || ((uintptr_t)qzeros[i] % 4) || (!out[i] && !(silu && i == 1)))
                 return BDQ_ERR_UNSUPPORTED;
             total_rb += (int)(OC[i] / 16);
         }
@@ -601,6 +618,11 @@ int bdq_gemv_w2_stream_launch(const void* x, int nmat, const int32_t* const* qwe
         m.pf_bytes[i] = pf ? (unsigned long long)prefetch_bytes[i] : 0ull;
     }
     if ((uintptr_t)x % 16) return BDQ_ERR_UNSUPPORTED;
+    if (silu && (nmat != 2 || OC[0] != OC[1])) {
+        set_error("gemv_w2: BDQ_GEMV_SILU_MUL takes exactly two matrices (gate, up) with equal out_features");
+        return BDQ_ERR_SHAPE;
+    }
+    m.silu = silu ? 1 : 0;
     const int nwin = (int)((IC / 128 + 3) / 4);
     const int wpw = (nwin + kSWarps - 1) / kSWarps;
     const bool pdl = (flags & BDQ_GEMV_PDL) != 0;
@@ -648,7 +670,8 @@ int bdq_gemv_w2_stream_launch(const void* x, int nmat, const int32_t* const* qwe
     }
     // two CTAs (16 warps) per SM; BDQ_GEMV_CTAS1 = one (leaves room for a PDL successor's CTA to prefetch)
     int grid = sm_count() * ((flags & BDQ_GEMV_CTAS1) ? 1 : 2);
-    if (grid > total_rb) grid = total_rb;
+    const int units = silu ? total_rb / 2 : total_rb;   // gate/up mode: CTAs own whole (gate, up) block pairs
+    if (grid > units) grid = units;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)grid);
     cfg.blockDim = dim3(kSThreads);
@@ -665,7 +688,7 @@ int bdq_gemv_w2_stream_launch(const void* x, int nmat, const int32_t* const* qwe
         g_gemv_prof_used += (size_t)grid * kSWarps * 16;
         if (g_gemv_prof_used > g_gemv_prof_cap) return BDQ_ERR_SHAPE;
     }
-    cudaLaunchKernelEx(&cfg, kern, (const __half*)x, m, (int)IC, zw, total_rb / grid, total_rb % grid, wpw, pbuf, prof ? ((flags >> 8) & 0xff) + 1 : 1,
+    cudaLaunchKernelEx(&cfg, kern, (const __half*)x, m, (int)IC, zw, units / grid, units % grid, wpw, pbuf, prof ? ((flags >> 8) & 0xff) + 1 : 1,
                        maps, depth);
     return check_launch("bdq_gemv_w2(stream)");
 }
@@ -683,7 +706,7 @@ extern "C" int bdq_gemv_w2_multi(const void* x, int nmat, const int32_t* const* 
         return BDQ_ERR_SHAPE;
     }
     for (int i = 0; i < nmat; ++i)
-        if (!qweight[i] || !scales[i] || !qzeros[i] || !out[i] || OC[i] <= 0) {
+        if (!qweight[i] || !scales[i] || !qzeros[i] || (!out[i] && !((flags & BDQ_GEMV_SILU_MUL) && i == 1)) || OC[i] <= 0) {
             set_error("gemv_w2_multi: matrix %d has a null pointer or OC <= 0", i);
             return BDQ_ERR_SHAPE;
         }
@@ -692,6 +715,10 @@ extern "C" int bdq_gemv_w2_multi(const void* x, int nmat, const int32_t* const* 
                                              n_prefetch, prefetch, prefetch_bytes, 0, nullptr)
                  : BDQ_ERR_UNSUPPORTED;
     if (rc != BDQ_ERR_UNSUPPORTED) return rc;
+    if (flags & BDQ_GEMV_SILU_MUL) {
+        set_error("gemv_w2_multi: BDQ_GEMV_SILU_MUL needs group 128, IC %% 128 == 0, OC %% 16 == 0 and 32-byte aligned weights");
+        return BDQ_ERR_UNSUPPORTED;
+    }
     for (int i = 0; i < nmat; ++i) {   // shapes the fused kernel does not take: one launch per matrix
         rc = bdq_gemv_w2(x, qweight[i], scales[i], qzeros[i], out[i], 1, IC, OC[i], group, flags | BDQ_GEMV_RING, stream);
         if (rc) return rc;

@@ -121,6 +121,7 @@ int bdq_pack_wq(const void* w_dq, const void* scales, const void* zeros, int32_t
 #define BDQ_GEMV_CTAS1 2 /* batch-1 streaming kernel: one CTA per SM instead of two (tuning knob) */
 #define BDQ_GEMV_RING 4  /* force the shared-memory ring kernel (the batch 2..8 path) also for batch 1 */
 #define BDQ_GEMV_TMA 16  /* batch-1 kernel: weight tiles through 2-D TMA + mbarriers instead of register loads */
+#define BDQ_GEMV_SILU_MUL 64 /* bdq_gemv_w2_multi with nmat = 2 (gate, up): out[0][i] = silu(gate_i) * up_i, out[1] unused */
 #define BDQ_GEMV_PROF 8  /* dev tool: record %globaltimer phase marks into the buffer given to bdq_gemv_set_prof */
 int bdq_gemv_set_prof(void* device_buf_u64, int64_t capacity_u64);
 int bdq_gemv_w2(const void* x, const int32_t* qweight, const void* scales, const int32_t* qzeros, void* out,

@@ -170,6 +170,71 @@ def test_gemv_w2_group64_generic_and_errors():
         E.gemv_forward_cuda(x.cpu(), qw, qs, qz, 2, 64)
 
 
+@pytest.mark.parametrize("oc,ic", [(12288, 4096), (11008, 4096), (48, 2176), (16, 128)])
+@pytest.mark.parametrize("flags", [0, 1, 16])
+def test_gemv_silu_mul_fused(oc, ic, flags):
+    """Fused gate/up launch with the SiLU-and-multiply epilogue (fused_mlp.py:44-108): equal, up to the last fp16 ulp of
+    the sigmoid, to the two stand-alone GEMVs followed by F.silu and the product (same kernel arithmetic per matrix)."""
+    from bitdistiller_b200 import awq_inference_engine as E
+    (gw, gz, gs), _ = _packed_layer(oc, ic, 300)
+    (uw, uz, us), _ = _packed_layer(oc, ic, 301)
+    x = torch.randn(1, ic, generator=torch.Generator().manual_seed(11)).to(torch.float16).to(dev)
+    out = E.gemv_silu_mul_forward_cuda(x, (gw, gs, gz), (uw, us, uz), 128, flags=flags)
+    g1 = E.gemv_forward_cuda(x, gw, gs, gz, 2, 128)
+    u1 = E.gemv_forward_cuda(x, uw, us, uz, 2, 128)
+    ref = torch.nn.functional.silu(g1) * u1
+    assert out.shape == (1, oc) and out.dtype == torch.float16
+    err = (out.float() - ref.float()).abs()
+    tol = 2.0 ** -9 * ref.float().abs() + 2.0 ** -24   # 2 fp16 ulps
+    assert not bool((err > tol).any()), (int((err > tol).sum()), float(err.max()))
+    assert float((out != ref).float().mean()) < 0.02   # and almost always bit-equal
+    if oc > 16:
+        with pytest.raises(ValueError):
+            E.gemv_silu_mul_forward_cuda(x, (gw, gs, gz), (uw[:16], us[:16], uz[:16]), 128)
+
+
+def test_quant_llama_mlp_matches_dequant():
+    """QuantLlamaMLP / make_fused_mlp (inference/modules/fused_mlp.py:18-133) for 1, 4 and 64 rows against the
+    dequantised fp32 MLP."""
+    from bitdistiller_b200.fused_mlp import QuantLlamaMLP, make_fused_mlp
+    from bitdistiller_b200.qmodule import WQLinear
+    from bitdistiller_b200.quantizer import pseudo_quantize_tensor
+    H, I = 1024, 2816
+
+    class MLP(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.gate_proj = torch.nn.Linear(H, I, bias=False, dtype=torch.float16, device=dev)
+            self.up_proj = torch.nn.Linear(H, I, bias=False, dtype=torch.float16, device=dev)
+            self.down_proj = torch.nn.Linear(I, H, bias=False, dtype=torch.float16, device=dev)
+
+    class Block(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.mlp = MLP()
+
+    blk = Block()
+    dq = {}
+    for i, name in enumerate(["gate_proj", "up_proj", "down_proj"]):
+        lin = getattr(blk.mlp, name)
+        lin.weight.data = make_weight("randn", lin.out_features, lin.in_features, torch.float16, 40 + i).to(dev) * (
+            (lin.in_features ** -0.5) / 0.02)
+        lin.weight.data, s, z = pseudo_quantize_tensor(lin.weight.data, n_bit=2, q_group_size=128, get_scale_zp=True)
+        dq[name] = lin.weight.data.float()
+        setattr(blk.mlp, name, WQLinear.from_linear(lin, 2, 128, False, s, z))
+    make_fused_mlp(blk)
+    assert isinstance(blk.mlp, QuantLlamaMLP)
+    assert {"gate_proj_qweight", "gate_proj_scales", "gate_proj_qzeros", "up_proj_qweight", "up_proj_scales",
+            "up_proj_qzeros"} <= set(dict(blk.mlp.named_buffers()))
+    for rows in (1, 4, 64):
+        x = torch.randn(1, rows, H, device=dev, dtype=torch.float16)
+        y = blk.mlp(x)
+        xf = x.float()
+        ref = (torch.nn.functional.silu(xf @ dq["gate_proj"].T) * (xf @ dq["up_proj"].T)) @ dq["down_proj"].T
+        assert y.shape == (1, rows, H)
+        assert float((y.float() - ref).norm() / ref.norm()) < 5e-3, rows
+
+
 def test_wqlinear_forward_decode_matches_dequant():
     """WQLinear end to end: real_quantize_model_weight-style construction, forward with 1 row and with bias."""
     from bitdistiller_b200.quantizer import pseudo_quantize_tensor

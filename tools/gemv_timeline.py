@@ -43,7 +43,9 @@ def main():
     for _ in range(3):
         gr.replay()
     torch.cuda.synchronize()
-    p = prof.cpu().numpy().astype(np.int64)
+    raw = prof.cpu().numpy().astype(np.uint64)
+    p = (raw & np.uint64(0xffffffffff)).astype(np.int64)          # %globaltimer ns (40 bits)
+    cyc = (raw >> np.uint64(40)).astype(np.int64)                   # SM clock (24 bits): per-warp deltas only
     nsm = torch.cuda.get_device_properties(dev).multi_processor_count
     grid_of = lambda rb: min(nsm * (1 if flags & 2 else 2), rb)
     # slabs in launch order
@@ -56,14 +58,15 @@ def main():
             n = 3 if nm == "q_proj" else (2 if nm == "gate_proj" else 1)
         rb = sum(o[7] for o in sel[i:i + n]) // 16
         g = grid_of(rb)
-        launches.append((QWEN3_8B[i % 7][0] if fused else which, g, p[off:off + g * 8 * 16].reshape(g, 8, 16)))
+        launches.append((QWEN3_8B[i % 7][0] if fused else which, g, p[off:off + g * 8 * 16].reshape(g, 8, 16),
+                         cyc[off:off + g * 8 * 16].reshape(g, 8, 16)))
         off += g * 8 * 16
         i += n
-    t0 = min(int(a[:, :, 0].min()) for _, _, a in launches)
+    t0 = min(int(a[:, :, 0].min()) for _, _, a, _ in launches)
     prev_end = None
     print("launch name      grid | first start, median start | median issue-done, wait-done, x-staged | median per-mark "
           "deltas ... | last end  (us, relative to the first launch; gaps vs previous launch's last end)")
-    for li, (nm, g, a) in enumerate(launches):
+    for li, (nm, g, a, cy) in enumerate(launches):
         a = a.astype(np.float64)
         valid = a > 0
         a = np.where(valid, (a - t0) * 1e-3, np.nan)
@@ -76,6 +79,13 @@ def main():
         print(f"{li:3d} {nm:10s} {g:4d} | {float(np.nanmin(st)):8.2f} {med(st):8.2f} | dur(max) {end - float(np.nanmin(st)):6.2f} | "
               + " ".join(f"{m:5.2f}" for m in marks) + f" | end {end:8.2f}{gap}")
         prev_end = end
+        # fine deltas between consecutive marks from the SM clock (cycles at 1.965 GHz -> ns), median and max over warps
+        dc = ((cy[:, :, 1:] - cy[:, :, :-1]) & 0xffffff).astype(np.float64) / 1.965
+        ok = valid[:, :, 1:] & valid[:, :, :-1]
+        dc = np.where(ok, dc, np.nan)
+        nm_ = [k for k in range(dc.shape[2]) if np.isfinite(dc[:, :, k]).any()]
+        print("      clk ns med: " + " ".join(f"{np.nanmedian(dc[:, :, k]):5.0f}" for k in nm_) +
+              "  | p95: " + " ".join(f"{np.nanpercentile(dc[:, :, k], 95):5.0f}" for k in nm_))
 
 
 if __name__ == "__main__":
