@@ -317,7 +317,7 @@ def secondary_metrics(torch, dev, peak):
     """BASELINE configs[3] and configs[4] at N=1: seconds for the int2-g128 clip search over all Llama-2-7B linears
     (tools/bench_multi.py) and tok/s of the Qwen3-8B packed int2 decode GEMV chain (tools/bench_gemv.py: CUDA graph +
     PDL, 4 fused launches per layer, dependent inputs, 1.859 GB of packed weights per token = L2-cold)."""
-    from tools import bench_gemv, bench_multi, bench_nf3
+    from tools import bench_gemv, bench_multi, bench_nf3, gemv_big
     out = {}
     nf = {r["kernel"]: r for r in bench_nf3.run(dev, peak)}
     out["nf3_g128_llama2_7b_layer"] = {
@@ -334,7 +334,12 @@ def secondary_metrics(torch, dev, peak):
     t = bench_gemv.graph_time(ops, 1, True, dev, True)
     out["gemv_int2_decode_qwen3_8b"] = {"tok_s": 1.0 / t, "us_per_token": t * 1e6, "bytes_per_token": nbytes,
                                         "frac_of_hbm_peak": nbytes / t / 1e9 / peak,
-                                        "mode": "CUDA graph + PDL, fused q/k/v and gate/up launches, L2 prefetch hint"}
+                                        "mode": "CUDA graph + PDL, fused q/k/v and gate/up launches, L2 prefetch hint; "
+                                                "144 dependent launches per token (latency-bound)"}
+    big = gemv_big.run(dev, peak, 1, shapes=((151936, 4096),))[0]
+    out["gemv_int2_kernel_streaming"] = {"shape": [big["OC"], big["IC"]], "mb": big["MB"], "us_per_launch": big["us_per_launch"],
+                                         "gbs": big["gbs"], "frac_of_hbm_peak": big["frac_of_hbm_peak"],
+                                         "what": "the same batch-1 kernel on one lm_head-sized launch (cold, distinct copies)"}
     return out
 
 
