@@ -1,5 +1,6 @@
 // Shared device helpers for the bdq kernels (sm_100a only).
 #pragma once
+#include <cstdlib>
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
@@ -14,6 +15,25 @@ constexpr int kF32 = BDQ_F32, kBF16 = BDQ_BF16, kF16 = BDQ_F16;
 void set_error(const char* fmt, ...);
 int check_launch(const char* what);
 int sm_count();
+
+// Grid of a persistent, warp-strided streaming kernel: a whole number of waves (resident CTAs per SM x SMs x waves), so
+// that no partial last wave leaves SMs idle.  Several short waves balance better than one long one (the SMs do not all
+// see the same HBM latency); measured optimum on B200: 16 waves for the int kernels, 6 for the NF3 ones (heavier
+// per-CTA prologue).  BDQ_FQ_WAVES overrides.
+template <typename Kern>
+static int wave_grid(Kern kern, int threads, int64_t blocks_needed, int default_waves) {
+    int occ = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, threads, 0) != cudaSuccess || occ < 1) occ = 4;
+    static int env_waves = -1;
+    if (env_waves < 0) {
+        const char* e = getenv("BDQ_FQ_WAVES");
+        env_waves = (e && atoi(e) > 0) ? atoi(e) : 0;
+    }
+    int64_t grid = (int64_t)sm_count() * occ * (env_waves ? env_waves : default_waves);
+    if (grid > blocks_needed) grid = blocks_needed;
+    if (grid < 1) grid = 1;
+    return (int)grid;
+}
 
 // ---- rounding of an fp32 "opmath" result to the logical tensor dtype (what eager PyTorch does between ops)
 template <int DT>

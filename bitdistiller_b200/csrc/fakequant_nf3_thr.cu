@@ -223,22 +223,18 @@ __global__ void __launch_bounds__(kNf3ThrThreads) nf3_thr_fwd_kernel(const uint8
     }
 }
 
-static int nf3_thr_grid(int64_t nchunk) {
-    int64_t blocks = ((nchunk + 31) / 32 + (kNf3ThrThreads / 32) - 1) / (kNf3ThrThreads / 32);
-    int64_t cap = (int64_t)sm_count() * 8;
-    if (blocks > cap) blocks = cap;
-    if (blocks < 1) blocks = 1;
-    return (int)blocks;
-}
+static int64_t nf3_thr_blocks(int64_t nchunk) { return ((nchunk + 31) / 32 + (kNf3ThrThreads / 32) - 1) / (kNf3ThrThreads / 32); }
 
 template <int DT, bool CLIP>
 static void nf3_thr_fwd_g(const uint8_t* w, uint8_t* dq, const void* cmin, const void* cmax, int64_t nchunk, int G,
                           const Nf3Tables& tab, cudaStream_t st) {
-    const int grid = nf3_thr_grid(nchunk);
+    const int64_t nb = nf3_thr_blocks(nchunk);
     const Nf3Stair stair = make_stair(tab, DT);
-    if (G == 128) nf3_thr_fwd_kernel<DT, 128, CLIP><<<grid, kNf3ThrThreads, 0, st>>>(w, dq, cmin, cmax, nchunk, tab, stair);
-    else if (G == 64) nf3_thr_fwd_kernel<DT, 64, CLIP><<<grid, kNf3ThrThreads, 0, st>>>(w, dq, cmin, cmax, nchunk, tab, stair);
-    else nf3_thr_fwd_kernel<DT, 32, CLIP><<<grid, kNf3ThrThreads, 0, st>>>(w, dq, cmin, cmax, nchunk, tab, stair);
+#define BDQ_L(GG) nf3_thr_fwd_kernel<DT, GG, CLIP><<<wave_grid(nf3_thr_fwd_kernel<DT, GG, CLIP>, kNf3ThrThreads, nb, 6), kNf3ThrThreads, 0, st>>>(w, dq, cmin, cmax, nchunk, tab, stair)
+    if (G == 128) BDQ_L(128);
+    else if (G == 64) BDQ_L(64);
+    else BDQ_L(32);
+#undef BDQ_L
 }
 
 // Returns true if the threshold kernel was launched (16-bit dtype, group 32/64/128, 32-byte aligned, no aux outputs).
@@ -429,12 +425,12 @@ bool launch_nf3_thr_bwd(const void* w, const void* gy, void* gw, int64_t n, int 
     if (((uintptr_t)w % 32) || ((uintptr_t)gy % 32) || ((uintptr_t)gw % 32) || (n % 128)) return false;
     const Nf3Tables tab = make_tables(dtype, sem);
     const int64_t nchunk = n / 32;
-    const int grid = nf3_thr_grid(nchunk);
+    const int64_t nb = nf3_thr_blocks(nchunk);
     if (dtype == kBF16) {
-        nf3_thr_bwd_kernel<kBF16><<<grid, kNf3ThrThreads, 0, st>>>((const uint8_t*)w, (const uint8_t*)gy, (uint8_t*)gw, nchunk,
+        nf3_thr_bwd_kernel<kBF16><<<wave_grid(nf3_thr_bwd_kernel<kBF16>, kNf3ThrThreads, nb, 6), kNf3ThrThreads, 0, st>>>((const uint8_t*)w, (const uint8_t*)gy, (uint8_t*)gw, nchunk,
                                                                     tab, make_stair(tab, kBF16));
     } else {
-        nf3_thr_bwd_kernel<kF16><<<grid, kNf3ThrThreads, 0, st>>>((const uint8_t*)w, (const uint8_t*)gy, (uint8_t*)gw, nchunk, tab,
+        nf3_thr_bwd_kernel<kF16><<<wave_grid(nf3_thr_bwd_kernel<kF16>, kNf3ThrThreads, nb, 6), kNf3ThrThreads, 0, st>>>((const uint8_t*)w, (const uint8_t*)gy, (uint8_t*)gw, nchunk, tab,
                                                                    make_stair(tab, kF16));
     }
     return true;

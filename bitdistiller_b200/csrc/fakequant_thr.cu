@@ -256,29 +256,27 @@ __global__ void __launch_bounds__(kThrThreads, 4) int_thr_bwd_kernel(const uint8
     }
 }
 
-static int thr_grid(int64_t nchunk) {
-    int64_t blocks = ((nchunk + 31) / 32 + (kThrThreads / 32) - 1) / (kThrThreads / 32);
-    const int64_t cap = (int64_t)sm_count() * 8;
-    if (blocks > cap) blocks = cap;
-    if (blocks < 1) blocks = 1;
-    return (int)blocks;
-}
+static int64_t thr_blocks(int64_t nchunk) { return ((nchunk + 31) / 32 + (kThrThreads / 32) - 1) / (kThrThreads / 32); }
 
 template <int DT, int RM, int NT, bool CLIP>
 static void thr_fwd_g(const uint8_t* w, uint8_t* dq, const void* cmin, const void* cmax, int64_t nchunk, int G, int sem,
                       cudaStream_t st) {
-    const int grid = thr_grid(nchunk);
-    if (G == 128) int_thr_fwd_kernel<DT, 128, RM, NT, CLIP><<<grid, kThrThreads, 0, st>>>(w, dq, cmin, cmax, nchunk, sem);
-    else if (G == 64) int_thr_fwd_kernel<DT, 64, RM, NT, CLIP><<<grid, kThrThreads, 0, st>>>(w, dq, cmin, cmax, nchunk, sem);
-    else int_thr_fwd_kernel<DT, 32, RM, NT, CLIP><<<grid, kThrThreads, 0, st>>>(w, dq, cmin, cmax, nchunk, sem);
+    const int64_t nb = thr_blocks(nchunk);
+#define BDQ_L(GG) int_thr_fwd_kernel<DT, GG, RM, NT, CLIP><<<wave_grid(int_thr_fwd_kernel<DT, GG, RM, NT, CLIP>, kThrThreads, nb, 16), kThrThreads, 0, st>>>(w, dq, cmin, cmax, nchunk, sem)
+    if (G == 128) BDQ_L(128);
+    else if (G == 64) BDQ_L(64);
+    else BDQ_L(32);
+#undef BDQ_L
 }
 
 template <int DT, int NT>
 static void thr_bwd_g(const uint8_t* w, const uint8_t* gy, uint8_t* gw, int64_t nchunk, int G, int sem, cudaStream_t st) {
-    const int grid = thr_grid(nchunk);
-    if (G == 128) int_thr_bwd_kernel<DT, 128, NT><<<grid, kThrThreads, 0, st>>>(w, gy, gw, nchunk, sem);
-    else if (G == 64) int_thr_bwd_kernel<DT, 64, NT><<<grid, kThrThreads, 0, st>>>(w, gy, gw, nchunk, sem);
-    else int_thr_bwd_kernel<DT, 32, NT><<<grid, kThrThreads, 0, st>>>(w, gy, gw, nchunk, sem);
+    const int64_t nb = thr_blocks(nchunk);
+#define BDQ_L(GG) int_thr_bwd_kernel<DT, GG, NT><<<wave_grid(int_thr_bwd_kernel<DT, GG, NT>, kThrThreads, nb, 16), kThrThreads, 0, st>>>(w, gy, gw, nchunk, sem)
+    if (G == 128) BDQ_L(128);
+    else if (G == 64) BDQ_L(64);
+    else BDQ_L(32);
+#undef BDQ_L
 }
 
 // Returns true if the threshold kernel was launched (16-bit dtype, bits 2 or 3, group 32/64/128, 32-byte aligned).

@@ -38,8 +38,11 @@ def run(dev, peak):
     def ifwd(i):
         lib.bdq_int_fakequant_fwd(L.ptr(ws[i]), L.ptr(out), None, None, None, None, None, n, 128, 2, 1, 1, 0, st)
 
+    def ibwd(i):
+        lib.bdq_int_ste_bwd(L.ptr(ws[i]), L.ptr(gs[i]), L.ptr(out), n, 128, 2, 1, 0, st)
+
     res = []
-    for name, fn, bpw in [("int2 fwd", ifwd, 4), ("nf3 fwd", nfwd, 4), ("nf3 fwd + clip (config 3)", nclip, 4 + 4 / 128),
+    for name, fn, bpw in [("int2 fwd", ifwd, 4), ("int2 ste bwd", ibwd, 6), ("nf3 fwd", nfwd, 4), ("nf3 fwd + clip (config 3)", nclip, 4 + 4 / 128),
                           ("nf3 ste bwd", nbwd, 6)]:
         t = timeit(fn, nbuf)
         gbs = N * bpw / t / 1e9
