@@ -314,7 +314,7 @@ __global__ void __launch_bounds__(kThreads) int_generic_kernel(
 
 static int grid_for(int64_t work_warps, int unroll) {
     int64_t blocks = (work_warps + (kThreads / 32) * unroll - 1) / ((kThreads / 32) * unroll);
-    int64_t cap = (int64_t)sm_count() * 8;
+    int64_t cap = (int64_t)sm_count() * 60;   // whole waves for 3, 4, 5 or 6 resident CTAs per SM (see wave_grid)
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
     return (int)blocks;
