@@ -22,12 +22,16 @@
 namespace bdq {
 
 constexpr int kGmM = 128, kGmN = 256, kGmK = 64;     // CTA tile; kGmK fp16 = one 128-byte swizzle row
-constexpr int kGmStages = 4;
-constexpr int kGmABytes = kGmM * kGmK * 2;           // 16 KB
+// MT = token tiles of 128 rows per CTA (1 or 2).  With MT = 2 the dequantised B stage feeds two accumulators (2 x 256 TMEM
+// columns = all of TMEM): the dequant work, which bounds the MT = 1 kernel, is amortised over twice the MMAs.
+constexpr int kGmABytes = kGmM * kGmK * 2;           // 16 KB per token tile
 constexpr int kGmBBytes = kGmN * kGmK * 2;           // 32 KB
-constexpr int kGmStageBytes = kGmABytes + kGmBBytes;
 constexpr int kGmThreads = 32 * 10;
-constexpr int kGmSmem = kGmStages * kGmStageBytes + 1024 /*alignment slack*/ + 256 /*barriers*/;
+template <int MT> struct GmCfg {
+    static constexpr int kStages = (MT == 1) ? 4 : 3;
+    static constexpr int kStageBytes = MT * kGmABytes + kGmBBytes;
+    static constexpr int kSmem = kStages * kStageBytes + 1024 /*alignment slack*/ + 256 /*barriers*/;
+};
 
 __device__ __forceinline__ uint32_t gm_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void gm_mbar_init(uint64_t* b, uint32_t count) {
@@ -112,12 +116,14 @@ struct GemmPeers {   // tensor parallel: this rank's column slice inside the pee
     int n;
 };
 
+template <int MT>
 __global__ void __launch_bounds__(kGmThreads, 1) gemm_w2_kernel(const __grid_constant__ CUtensorMap xmap,
                                                                 const uint32_t* __restrict__ qweight,
                                                                 const __half* __restrict__ scales,
                                                                 const uint32_t* __restrict__ qzeros, __half* __restrict__ out,
                                                                 int M, int IC, int OC, int G, int zw, int ldo,
                                                                 const GemmPeers peers) {
+    constexpr int kGmStages = GmCfg<MT>::kStages, kGmStageBytes = GmCfg<MT>::kStageBytes;
     extern __shared__ uint8_t gm_smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(gm_smem_raw) + 1023) & ~(uintptr_t)1023);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kGmStages * kGmStageBytes);
@@ -128,7 +134,7 @@ __global__ void __launch_bounds__(kGmThreads, 1) gemm_w2_kernel(const __grid_con
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3 * kGmStages + 1);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int n0 = blockIdx.x * kGmN, m0 = blockIdx.y * kGmM;
+    const int n0 = blockIdx.x * kGmN, m0 = blockIdx.y * (kGmM * MT);
     const int nkb = IC / kGmK;
 
     if (tid == 0) {
@@ -142,7 +148,7 @@ __global__ void __launch_bounds__(kGmThreads, 1) gemm_w2_kernel(const __grid_con
         asm volatile("prefetch.tensormap [%0];" ::"l"(&xmap) : "memory");
     }
     if (warp == 1) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(gm_smem_u32(tmem_slot)), "r"(256) : "memory");
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(gm_smem_u32(tmem_slot)), "r"(256 * MT) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -151,12 +157,12 @@ __global__ void __launch_bounds__(kGmThreads, 1) gemm_w2_kernel(const __grid_con
     const uint32_t tmem_d = *tmem_slot;
 
     if (warp == 0) {
-        // ================= TMA producer: x tile [128 tokens x 64 k] per stage =================
+        // ================= TMA producer: x tile [128 * MT tokens x 64 k] per stage (one box) =================
         if (lane == 0) {
             for (int kb = 0; kb < nkb; ++kb) {
                 const int s = kb % kGmStages;
                 if (kb >= kGmStages) gm_mbar_wait(&empty[s], ((kb / kGmStages) - 1) & 1);
-                gm_mbar_expect_tx(&full_a[s], kGmABytes);
+                gm_mbar_expect_tx(&full_a[s], MT * kGmABytes);
                 gm_tma_load_2d(smem + s * kGmStageBytes, &xmap, kb * kGmK, m0, &full_a[s]);
             }
         }
@@ -170,10 +176,14 @@ __global__ void __launch_bounds__(kGmThreads, 1) gemm_w2_kernel(const __grid_con
                 gm_mbar_wait(&full_b[s], ph);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const uint32_t a_addr = gm_smem_u32(smem + s * kGmStageBytes);
-                const uint64_t adesc = gm_desc(a_addr), bdesc = gm_desc(a_addr + kGmABytes);
+                const uint64_t bdesc = gm_desc(a_addr + MT * kGmABytes);
 #pragma unroll
-                for (int k = 0; k < kGmK / 16; ++k)   // advance 32 bytes (>> 4 = 2) inside the swizzle row per K = 16
-                    gm_mma(tmem_d, adesc + 2 * k, bdesc + 2 * k, kGmIdesc, (kb | k) != 0 ? 1u : 0u);
+                for (int mt = 0; mt < MT; ++mt) {
+                    const uint64_t adesc = gm_desc(a_addr + mt * kGmABytes);
+#pragma unroll
+                    for (int k = 0; k < kGmK / 16; ++k)   // advance 32 bytes (>> 4 = 2) inside the swizzle row per K = 16
+                        gm_mma(tmem_d + mt * 256, adesc + 2 * k, bdesc + 2 * k, kGmIdesc, (kb | k) != 0 ? 1u : 0u);
+                }
                 gm_commit(&empty[s]);                 // frees the stage when these MMAs have read it
             }
             gm_commit(tmem_full);                     // accumulator complete
@@ -222,7 +232,7 @@ __global__ void __launch_bounds__(kGmThreads, 1) gemm_w2_kernel(const __grid_con
                 for (int w4 = 0; w4 < 4; ++w4) gm_dequant16(cur.r[h * 4 + w4], s2, kz1024, kz64, kz4, o + w4 * 8);
                 const int s = kb % kGmStages;
                 if (kb >= kGmStages) gm_mbar_wait(&empty[s], ((kb / kGmStages) - 1) & 1);
-                uint8_t* brow = smem + s * kGmStageBytes + kGmABytes + j * 128;
+                uint8_t* brow = smem + s * kGmStageBytes + MT * kGmABytes + j * 128;
 #pragma unroll
                 for (int c = 0; c < 8; ++c)   // 16-byte chunk c of row j lives at chunk position c ^ (j % 8)
                     *reinterpret_cast<uint4*>(brow + ((c ^ (j & 7)) << 4)) = make_uint4(o[4 * c], o[4 * c + 1], o[4 * c + 2], o[4 * c + 3]);
@@ -238,12 +248,13 @@ __global__ void __launch_bounds__(kGmThreads, 1) gemm_w2_kernel(const __grid_con
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const int lane_grp = warp & 3;               // this warp may only touch TMEM lanes [32*(warp%4), +32)
         const int col_half = (warp - 2) >> 2;        // 0: columns 0..127, 1: columns 128..255
-        const int row = m0 + lane_grp * 32 + lane;   // token
 #pragma unroll 1
-        for (int cb = 0; cb < 4; ++cb) {
+        for (int cbi = 0; cbi < 4 * MT; ++cbi) {
+            const int mt = cbi >> 2, cb = cbi & 3;
+            const int row = m0 + mt * kGmM + lane_grp * 32 + lane;   // token
             const int col = col_half * 128 + cb * 32;
             uint32_t r[32];
-            const uint32_t taddr = tmem_d + ((uint32_t)(lane_grp * 32) << 16) + (uint32_t)col;
+            const uint32_t taddr = tmem_d + ((uint32_t)(lane_grp * 32) << 16) + (uint32_t)(mt * 256 + col);
             asm volatile(
                 "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
@@ -273,7 +284,7 @@ __global__ void __launch_bounds__(kGmThreads, 1) gemm_w2_kernel(const __grid_con
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
-    if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(256) : "memory");
+    if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(256 * MT) : "memory");
 }
 
 // cuTensorMapEncodeTiled through the runtime's driver entry point lookup (libbdq.so must load on machines without a driver)
@@ -303,7 +314,10 @@ int launch_gemm_w2(const void* x, const int32_t* qweight, const void* scales, co
     CUtensorMap map;
     const cuuint64_t dims[2] = {(cuuint64_t)IC, (cuuint64_t)M};          // innermost first
     const cuuint64_t strides[1] = {(cuuint64_t)IC * 2};                   // bytes, dims 1..rank-1
-    const cuuint32_t box[2] = {(cuuint32_t)kGmK, (cuuint32_t)kGmM};
+    // two token tiles per CTA when there is a second one to fill and the grid still covers at least half of the SMs
+    const int64_t ctas2 = ((OC + kGmN - 1) / kGmN) * ((M + 2 * kGmM - 1) / (2 * kGmM));
+    const int MT = (M > kGmM && ctas2 * 2 >= sm_count()) ? 2 : 1;
+    const cuuint32_t box[2] = {(cuuint32_t)kGmK, (cuuint32_t)(kGmM * MT)};
     const cuuint32_t estr[2] = {1, 1};
     CUresult r = enc(&map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(x), dims, strides, box, estr,
                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
@@ -311,13 +325,20 @@ int launch_gemm_w2(const void* x, const int32_t* qweight, const void* scales, co
     if (r != CUDA_SUCCESS) { set_error("gemm_w2: cuTensorMapEncodeTiled failed (%d)", (int)r); return BDQ_ERR_CUDA; }
     static bool attr_done = false;
     if (!attr_done) {
-        if (cudaFuncSetAttribute(gemm_w2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kGmSmem) != cudaSuccess)
+        if (cudaFuncSetAttribute(gemm_w2_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, GmCfg<1>::kSmem) != cudaSuccess ||
+            cudaFuncSetAttribute(gemm_w2_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, GmCfg<2>::kSmem) != cudaSuccess)
             return check_launch("bdq_gemm_w2(attr)");
         attr_done = true;
     }
-    dim3 grid((unsigned)((OC + kGmN - 1) / kGmN), (unsigned)((M + kGmM - 1) / kGmM));
-    gemm_w2_kernel<<<grid, kGmThreads, kGmSmem, st>>>(map, (const uint32_t*)qweight, (const __half*)scales, (const uint32_t*)qzeros,
-                                                      (__half*)out, (int)M, (int)IC, (int)OC, group, zw, (int)ldo, peers);
+    dim3 grid((unsigned)((OC + kGmN - 1) / kGmN), (unsigned)((M + kGmM * MT - 1) / (kGmM * MT)));
+    if (MT == 2)
+        gemm_w2_kernel<2><<<grid, kGmThreads, GmCfg<2>::kSmem, st>>>(map, (const uint32_t*)qweight, (const __half*)scales,
+                                                                     (const uint32_t*)qzeros, (__half*)out, (int)M, (int)IC, (int)OC,
+                                                                     group, zw, (int)ldo, peers);
+    else
+        gemm_w2_kernel<1><<<grid, kGmThreads, GmCfg<1>::kSmem, st>>>(map, (const uint32_t*)qweight, (const __half*)scales,
+                                                                     (const uint32_t*)qzeros, (__half*)out, (int)M, (int)IC, (int)OC,
+                                                                     group, zw, (int)ldo, peers);
     return check_launch("bdq_gemm_w2");
 }
 

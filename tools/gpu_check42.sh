@@ -1,0 +1,3 @@
+#!/bin/bash
+timeout 1500 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
+timeout 300 python tools/microbench.py 2>&1 | grep "f32"
