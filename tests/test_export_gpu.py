@@ -72,3 +72,22 @@ def test_real_quantize_export_load_roundtrip():
     f1, f12 = skel(ids1).logits.float(), skel(ids12).logits.float()
     assert float((f1 - out1).norm() / out1.norm()) < 5e-3
     assert float((f12 - out12).norm() / out12.norm()) < 5e-3
+
+
+@torch.no_grad()
+def test_fused_qkv_linear_equals_separate():
+    """fused_attn.py:312-337: one WQLinear over the concatenated packed buffers == the three projections, decode and prefill."""
+    from bitdistiller_b200.fused_attn import fuse_qkv_linear, split_qkv
+    from bitdistiller_b200.quantizer import real_quantize_model_weight
+    dev = torch.device("cuda:0")
+    m = _tiny_llama(2)
+    real_quantize_model_weight(m, 2, {"zero_point": True, "q_group_size": 128})
+    att = m.model.layers[0].self_attn.to(dev)
+    qkv = fuse_qkv_linear(att.q_proj, att.k_proj, att.v_proj)
+    assert qkv.out_features == 3 * 256 and tuple(qkv.qweight.shape) == (768, 16)
+    for rows in (1, 5, 40):
+        x = torch.randn(1, rows, 256, device=dev, dtype=torch.float16)
+        q, k, v = split_qkv(qkv(x), 256, 256, 256)
+        for got, proj in ((q, att.q_proj), (k, att.k_proj), (v, att.v_proj)):
+            ref = proj(x)
+            assert float((got.float() - ref.float()).norm() / ref.float().norm()) < 2e-3, rows
