@@ -144,6 +144,25 @@ int bdq_gemv_w2_multi(const void* x, int nmat, const int32_t* const* qweight, co
                       int n_prefetch, const void* const* prefetch, const int64_t* prefetch_bytes, bdq_stream_t stream);
 
 /*
+ * Packed NF3 (3 bits per weight + two fp16 scales per group).  The reference has no packed NF3 format or kernel
+ * (quantization/qmodule.py:77 accepts w_bit 2 and 4 only), so the layout is this library's own; its contract is that
+ * bdq_nf3_dequant(pack(w)) equals SteN2F3Quantizer.forward(w) / pseudo_quantize_n2f3_tensor(w)
+ * (quantization/quantizer.py:113-116,184-242) bit for bit in fp16.
+ *   level index e = position in the ascending staircase -1, -0.535, -0.247, 0, 0.183, 0.382, 0.623, 1
+ *   qweight int32 [rows, cols/16]: bits [2i, 2i+2) of word c = low two bits of e of column 16c + i
+ *   qhigh   int32 [rows, cols/32]: bit 16w + i of word c = high bit of e of column 32c + 16w + i
+ *   scales  fp16  [rows, 2*cols/group]: (|group max|, |group min|) per group; e < 3 uses the second one
+ * bdq_pack_nf3 takes the uint8 codes written by bdq_nf3_fakequant_fwd (cols % 32 == 0, 16-byte aligned).
+ * bdq_gemv_nf3: out[b, oc] = fp16(sum_k x[b,k] * level * scale), x [B, IC] fp16, fp32 accumulation; first version
+ * (CUDA-core table decode).  group % 32 == 0, IC % group == 0.
+ */
+int bdq_pack_nf3(const uint8_t* codes, int32_t* qweight, int32_t* qhigh, int64_t rows, int64_t cols, bdq_stream_t stream);
+int bdq_nf3_dequant(const int32_t* qweight, const int32_t* qhigh, const void* scales, void* out_f16, int64_t rows, int64_t cols,
+                    int group, bdq_stream_t stream);
+int bdq_gemv_nf3(const void* x, const int32_t* qweight, const int32_t* qhigh, const void* scales, void* out, int64_t B,
+                 int64_t IC, int64_t OC, int group, bdq_stream_t stream);
+
+/*
  * Packed 2-bit prefill GEMM: out[m, oc] = fp16( sum_k x[m,k] * fp16(scales[oc,k/G] * (code[oc,k] - zero[oc,k/G])) ),
  * fp32 accumulation in tensor memory (tcgen05.mma, TMA-fed activations, in-register dequant of the packed weights).
  * Replaces quant_matmul_v2 (quantization/triton_kernels.py:102-134) and gemm_forward_cuda (pybind.cpp:12; the
