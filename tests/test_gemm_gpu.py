@@ -43,7 +43,9 @@ def _check(out, ref, x, dqw):
 
 @pytest.mark.parametrize("m,oc,ic,G", [(128, 256, 128, 128), (256, 512, 1024, 128), (2048, 4096, 4096, 128),
                                        (200, 256, 11008, 128), (77, 1024, 4096, 128), (384, 512, 2048, 64),
-                                       (300, 128, 4096, 128), (130, 352, 1024, 128), (64, 64, 512, 128)])   # partial last N tile
+                                       (300, 128, 4096, 128), (130, 352, 1024, 128), (64, 64, 512, 128),   # partial last N tile
+                                       # two token tiles per CTA (grids that cover >= half the SMs): ragged second tile
+                                       (257, 12288, 512, 128), (129, 20480, 256, 128), (1000, 4096, 1024, 64)])
 def test_gemm_w2_tcgen05_vs_reference_math(m, oc, ic, G):
     from bitdistiller_b200.triton_kernels import gemm_w2
     (qw, qz, qs), dq = _packed_layer(oc, ic, 5, G)
