@@ -16,8 +16,7 @@
 
 namespace bdq {
 
-constexpr int kAcThreads = 256;
-constexpr int kAcWarps = 8;
+constexpr int kAcMaxWarps = 16;
 constexpr int kAcRows = 112;   // candidate rows (7 MMA row tiles): nc*nc candidates + the weight row
 constexpr int kAcOT = 64;      // output channels per CTA
 
@@ -26,6 +25,11 @@ struct AcCfg {
     static constexpr int KMUL = (DT == kF32) ? 3 : 1;      // K expansion of the hi/lo split
     static constexpr int TCH = (DT == kF32) ? 128 : 512;   // tokens staged per pass
     static constexpr bool F16 = (DT == kF16);              // MMA operand type: f16, else bf16
+    // 16 warps for the 16-bit dtypes: the kernel holds one CTA per SM (the staged X tile fills shared memory) and its
+    // phases are separated by barriers, so the warp count is what hides latency; 32 tokens per warp also halves the
+    // accumulator registers (128 registers per thread at 512 threads = the whole register file)
+    static constexpr int WARPS = (DT == kF32) ? 8 : 16;
+    static constexpr int THREADS = WARPS * 32;
 };
 
 __device__ __forceinline__ void ldsm_x4(uint32_t* r, const void* p) {
@@ -59,7 +63,7 @@ __host__ __device__ inline AcSmem ac_layout(int G, int kmul, int tch) {
     L.xs = 0;
     L.as = L.xs + tch * L.pitch;
     L.errw = L.as + kAcRows * L.pitch;
-    L.errsum = L.errw + kAcWarps * kAcRows * 4;
+    L.errsum = L.errw + kAcMaxWarps * kAcRows * 4;
     L.cand = L.errsum + kAcOT * kAcRows * 4;
     L.wf = L.cand + kAcRows * 8 * 4;
     L.wred = L.wf + 128 * 4;
@@ -80,10 +84,11 @@ struct AcArgs {
 };
 
 template <int DT>
-__global__ void __launch_bounds__(kAcThreads, 1) autoclip_kernel(const AcArgs a) {
+__global__ void __launch_bounds__(AcCfg<DT>::THREADS, 1) autoclip_kernel(const AcArgs a) {
     using C = AcCfg<DT>;
     constexpr bool F16 = C::F16;
-    constexpr int NTW = C::TCH / 64;   // 8-token MMA column tiles per warp
+    constexpr int kAcThreads = C::THREADS, kAcWarps = C::WARPS;
+    constexpr int NTW = C::TCH / (8 * kAcWarps);   // 8-token MMA column tiles per warp
     extern __shared__ __align__(128) uint8_t smem[];
     const int G = a.G, KX = G * C::KMUL;
     const AcSmem L = ac_layout(G, C::KMUL, C::TCH);
@@ -308,7 +313,7 @@ static int launch_autoclip(const AcArgs& a, cudaStream_t st) {
         attr_done = true;
     }
     dim3 grid((unsigned)(a.ci / a.G), (unsigned)((a.co + kAcOT - 1) / kAcOT));
-    autoclip_kernel<DT><<<grid, kAcThreads, (size_t)L.total, st>>>(a);
+    autoclip_kernel<DT><<<grid, C::THREADS, (size_t)L.total, st>>>(a);
     return check_launch("bdq_autoclip");
 }
 
