@@ -13,6 +13,7 @@
 #include "bdq_common.cuh"
 #include "fq_int_elem.cuh"
 #include "fq_nf3_elem.cuh"
+#include "fakequant_thr.cuh"
 
 namespace bdq {
 
@@ -65,7 +66,7 @@ __host__ __device__ inline AcSmem ac_layout(int G, int kmul, int tch) {
     L.errw = L.as + kAcRows * L.pitch;
     L.errsum = L.errw + kAcMaxWarps * kAcRows * 4;
     L.cand = L.errsum + kAcOT * kAcRows * 4;
-    L.wf = L.cand + kAcRows * 8 * 4;
+    L.wf = L.cand + kAcRows * 12 * 4;
     L.wred = L.wf + 128 * 4;
     L.total = L.wred + 64;
     return L;
@@ -104,7 +105,7 @@ __global__ void __launch_bounds__(AcCfg<DT>::THREADS, 1) autoclip_kernel(const A
     uint8_t* As = smem + L.as;
     float* errw = reinterpret_cast<float*>(smem + L.errw);
     float* errsum = reinterpret_cast<float*>(smem + L.errsum);
-    float* cand = reinterpret_cast<float*>(smem + L.cand);   // [row][8]: int: s, y, z, t1, lo, hi | nf3: sp, sn, yp, yn, lo, hi, nan
+    float* cand = reinterpret_cast<float*>(smem + L.cand);   // [row][12]: int: s, y, z, t1, lo, hi, -, pass, T1, T2, T3, thr_ok | nf3: sp, sn, yp, yn, lo, hi, nan, pass
     float* wf = reinterpret_cast<float*>(smem + L.wf);
     float* wred = reinterpret_cast<float*>(smem + L.wred);
 
@@ -149,7 +150,8 @@ __global__ void __launch_bounds__(AcCfg<DT>::THREADS, 1) autoclip_kernel(const A
             if (tid <= nc2) {
                 float mx = wred[0], mn = wred[1];
                 for (int i = 1; i < G / 32; ++i) { mx = fmaxf(mx, wred[2 * i]); mn = fminf(mn, wred[2 * i + 1]); }
-                float* cp = cand + tid * 8;
+                float* cp = cand + tid * 12;
+                cp[11] = 0.f;
                 if (tid == nc2) {
                     cp[4] = -INFINITY; cp[5] = INFINITY; cp[7] = 1.f;   // weight row: pass-through
                 } else {
@@ -162,6 +164,20 @@ __global__ void __launch_bounds__(AcCfg<DT>::THREADS, 1) autoclip_kernel(const A
                     if (a.quant_type == BDQ_QUANT_INT) {
                         const IntQ p = int_group_params<DT>(cmx, cmn, qmax, a.sem);
                         cp[0] = p.s; cp[1] = p.y; cp[2] = p.z; cp[3] = p.t1;
+                        if constexpr (DT != kF32) {
+                            // 2-bit candidates in threshold form (fakequant_thr.cuh: exact, verified thresholds): the row
+                            // is then written with packed compares instead of the op-by-op quantiser
+                            if (a.bits == 2) {
+                                bool ok = fmaxf(fabsf(cmx), fabsf(cmn)) * p.y < 1e30f;
+#pragma unroll
+                                for (int k = 0; k < 3; ++k) {
+                                    bool o;
+                                    cp[8 + k] = find_threshold<DT, BDQ_ROUND_HALF_EVEN>(-p.z + (float)(k + 1), p, o);
+                                    ok = ok && o;
+                                }
+                                cp[11] = ok ? 1.f : 0.f;
+                            }
+                        }
                     } else {
                         const Nf3Q p = nf3_group_params(cmx, cmn);
                         cp[0] = p.sp; cp[1] = p.sn; cp[2] = p.yp; cp[3] = p.yn; cp[6] = p.nan_group ? 1.f : 0.f;
@@ -172,7 +188,18 @@ __global__ void __launch_bounds__(AcCfg<DT>::THREADS, 1) autoclip_kernel(const A
             // ---- (c) candidate rows of A: Q(clamp(w, lo, hi)) with the reference's T roundings
             for (int i = tid; i < (nc2 + 1) * (G / 2); i += kAcThreads) {
                 const int c = i / (G / 2), j = i - c * (G / 2);
-                const float* cp = cand + c * 8;
+                const float* cp = cand + c * 12;
+                if constexpr (DT != kF32) {
+                    if (cp[11] != 0.f) {   // threshold form: clamp, count the thresholds passed, (count - z) * s
+                        using P = P2<DT>;
+                        using h2 = typename P::h2;
+                        const h2 x2 = __hmin2(__hmax2(P::pack(wf[2 * j], wf[2 * j + 1]), P::dup(cp[4])), P::dup(cp[5]));
+                        const h2 c2 = __hadd2(__hadd2(__hge2(x2, P::dup(cp[8])), __hge2(x2, P::dup(cp[9]))), __hge2(x2, P::dup(cp[10])));
+                        const h2 q2 = __hmul2(__hadd2(c2, P::dup(-cp[2])), P::dup(cp[0]));   // rT((c - z) * s)
+                        reinterpret_cast<uint32_t*>(As + (size_t)c * L.pitch)[j] = P::bits(q2);
+                        continue;
+                    }
+                }
                 float v[2];
 #pragma unroll
                 for (int e = 0; e < 2; ++e) {
