@@ -241,7 +241,7 @@ __global__ void __launch_bounds__(AcCfg<DT>::THREADS, 1) autoclip_kernel(const A
                 for (int n = 0; n < NTW; ++n) acc[n][0] = acc[n][1] = acc[n][2] = acc[n][3] = 0.f;
                 const uint8_t* arow = As + (size_t)(mt * 16 + (lane & 15)) * L.pitch + (lane >> 4) * 16;
                 const uint8_t* brow = Xs + (size_t)(warp * 8 * NTW + (lane & 7) + ((lane >> 4) << 3)) * L.pitch + ((lane >> 3) & 1) * 16;
-#pragma unroll 2
+#pragma unroll 4
                 for (int k0 = 0; k0 < KX; k0 += 16) {
                     uint32_t af[4];
                     ldsm_x4(af, arow + k0 * 2);
