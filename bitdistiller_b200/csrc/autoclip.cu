@@ -136,6 +136,21 @@ __global__ void __launch_bounds__(AcCfg<DT>::THREADS, 1) autoclip_kernel(const A
             }
         }
 
+        // 16-bit dtypes: this warp's X fragments (its 32 tokens x K <= 128) do not depend on the channel: load them once per
+        // staged chunk and keep them in registers (64), so the contraction issues one ldmatrix per 4 MMAs instead of 3
+        constexpr int KS = (DT == kF32) ? 1 : 8, NP = (DT == kF32) ? 1 : NTW / 2;
+        uint32_t bfr[KS][NP][4];
+        if constexpr (DT != kF32) {
+            __syncthreads();
+            const uint8_t* brow = Xs + (size_t)(warp * 8 * NTW + (lane & 7) + ((lane >> 4) << 3)) * L.pitch + ((lane >> 3) & 1) * 16;
+#pragma unroll
+            for (int ks = 0; ks < KS; ++ks)
+#pragma unroll
+                for (int np = 0; np < NP; ++np) {
+                    if (ks * 16 < KX) ldsm_x4(bfr[ks][np], brow + (size_t)np * 16 * L.pitch + ks * 32);
+                    else bfr[ks][np][0] = bfr[ks][np][1] = bfr[ks][np][2] = bfr[ks][np][3] = 0u;
+                }
+        }
         for (int ol = 0; ol < no; ++ol) {
             const int64_t o = o0 + ol;
             // ---- (a) the weight group and its extremes
@@ -186,20 +201,25 @@ __global__ void __launch_bounds__(AcCfg<DT>::THREADS, 1) autoclip_kernel(const A
             }
             __syncthreads();
             // ---- (c) candidate rows of A: Q(clamp(w, lo, hi)) with the reference's T roundings
-            for (int i = tid; i < (nc2 + 1) * (G / 2); i += kAcThreads) {
-                const int c = i / (G / 2), j = i - c * (G / 2);
-                const float* cp = cand + c * 12;
-                if constexpr (DT != kF32) {
-                    if (cp[11] != 0.f) {   // threshold form: clamp, count the thresholds passed, (count - z) * s
-                        using P = P2<DT>;
-                        using h2 = typename P::h2;
-                        const h2 x2 = __hmin2(__hmax2(P::pack(wf[2 * j], wf[2 * j + 1]), P::dup(cp[4])), P::dup(cp[5]));
-                        const h2 c2 = __hadd2(__hadd2(__hge2(x2, P::dup(cp[8])), __hge2(x2, P::dup(cp[9]))), __hge2(x2, P::dup(cp[10])));
-                        const h2 q2 = __hmul2(__hadd2(c2, P::dup(-cp[2])), P::dup(cp[0]));   // rT((c - z) * s)
-                        reinterpret_cast<uint32_t*>(As + (size_t)c * L.pitch)[j] = P::bits(q2);
-                        continue;
-                    }
-                }
+            // (16 threads per row: the row's parameters are read once, not once per element pair)
+            for (int c = tid >> 4; c <= nc2; c += kAcThreads / 16) {
+              const float* cp = cand + c * 12;
+              if constexpr (DT != kF32) {
+                  if (cp[11] != 0.f) {   // threshold form: clamp, count the thresholds passed, (count - z) * s
+                      using P = P2<DT>;
+                      using h2 = typename P::h2;
+                      const h2 lo2 = P::dup(cp[4]), hi2 = P::dup(cp[5]), t1 = P::dup(cp[8]), t2 = P::dup(cp[9]), t3 = P::dup(cp[10]);
+                      const h2 nz2 = P::dup(-cp[2]), s2 = P::dup(cp[0]);
+                      uint32_t* arow = reinterpret_cast<uint32_t*>(As + (size_t)c * L.pitch);
+                      for (int j = tid & 15; j < G / 2; j += 16) {
+                          const h2 x2 = __hmin2(__hmax2(P::pack(wf[2 * j], wf[2 * j + 1]), lo2), hi2);
+                          const h2 c2 = __hadd2(__hadd2(__hge2(x2, t1), __hge2(x2, t2)), __hge2(x2, t3));
+                          arow[j] = P::bits(__hmul2(__hadd2(c2, nz2), s2));   // rT((c - z) * s)
+                      }
+                      continue;
+                  }
+              }
+              for (int j = tid & 15; j < G / 2; j += 16) {
                 float v[2];
 #pragma unroll
                 for (int e = 0; e < 2; ++e) {
@@ -228,6 +248,7 @@ __global__ void __launch_bounds__(AcCfg<DT>::THREADS, 1) autoclip_kernel(const A
                 } else {
                     reinterpret_cast<uint32_t*>(row)[j] = enc16<F16>(v[0]) | ((uint32_t)enc16<F16>(v[1]) << 16);
                 }
+              }
             }
             __syncthreads();
             // ---- (d) tensor-core contraction: this warp owns tokens [warp*8*NTW, +8*NTW) of the staged chunk
@@ -241,16 +262,31 @@ __global__ void __launch_bounds__(AcCfg<DT>::THREADS, 1) autoclip_kernel(const A
                 for (int n = 0; n < NTW; ++n) acc[n][0] = acc[n][1] = acc[n][2] = acc[n][3] = 0.f;
                 const uint8_t* arow = As + (size_t)(mt * 16 + (lane & 15)) * L.pitch + (lane >> 4) * 16;
                 const uint8_t* brow = Xs + (size_t)(warp * 8 * NTW + (lane & 7) + ((lane >> 4) << 3)) * L.pitch + ((lane >> 3) & 1) * 16;
-#pragma unroll 4
-                for (int k0 = 0; k0 < KX; k0 += 16) {
-                    uint32_t af[4];
-                    ldsm_x4(af, arow + k0 * 2);
+                if constexpr (DT != kF32) {
 #pragma unroll
-                    for (int n = 0; n < NTW; n += 2) {
-                        uint32_t bf[4];
-                        ldsm_x4(bf, brow + (size_t)n * 8 * L.pitch + k0 * 2);
-                        mma_ac<F16>(acc[n], af, bf[0], bf[1]);
-                        mma_ac<F16>(acc[n + 1], af, bf[2], bf[3]);
+                    for (int ks = 0; ks < KS; ++ks) {
+                        if (ks * 16 < KX) {
+                            uint32_t af[4];
+                            ldsm_x4(af, arow + ks * 32);
+#pragma unroll
+                            for (int np = 0; np < NP; ++np) {
+                                mma_ac<F16>(acc[2 * np], af, bfr[ks][np][0], bfr[ks][np][1]);
+                                mma_ac<F16>(acc[2 * np + 1], af, bfr[ks][np][2], bfr[ks][np][3]);
+                            }
+                        }
+                    }
+                } else {
+#pragma unroll 4
+                    for (int k0 = 0; k0 < KX; k0 += 16) {
+                        uint32_t af[4];
+                        ldsm_x4(af, arow + k0 * 2);
+#pragma unroll
+                        for (int n = 0; n < NTW; n += 2) {
+                            uint32_t bf[4];
+                            ldsm_x4(bf, brow + (size_t)n * 8 * L.pitch + k0 * 2);
+                            mma_ac<F16>(acc[n], af, bf[0], bf[1]);
+                            mma_ac<F16>(acc[n + 1], af, bf[2], bf[3]);
+                        }
                     }
                 }
                 if (mi == 0) {
