@@ -22,8 +22,20 @@ int sm_count();
 // per-CTA prologue).  BDQ_FQ_WAVES overrides.
 template <typename Kern>
 static int wave_grid(Kern kern, int threads, int64_t blocks_needed, int default_waves) {
+    // occupancy per kernel address, cached (all instantiations with one signature share this template instance); a benign
+    // race at worst repeats the query
+    static const void* seen[64];
+    static int seen_occ[64];
+    static int nseen = 0;
     int occ = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, threads, 0) != cudaSuccess || occ < 1) occ = 4;
+    const void* key = reinterpret_cast<const void*>(kern);
+    for (int i = 0; i < nseen && i < 64; ++i)
+        if (seen[i] == key) { occ = seen_occ[i]; break; }
+    if (occ < 1) {
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, threads, 0) != cudaSuccess || occ < 1) occ = 4;
+        const int slot = nseen;
+        if (slot < 64) { seen[slot] = key; seen_occ[slot] = occ; nseen = slot + 1; }
+    }
     static int env_waves = -1;
     if (env_waves < 0) {
         const char* e = getenv("BDQ_FQ_WAVES");
