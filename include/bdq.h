@@ -163,6 +163,24 @@ int bdq_gemv_nf3(const void* x, const int32_t* qweight, const int32_t* qhigh, co
                  int64_t IC, int64_t OC, int group, bdq_stream_t stream);
 
 /*
+ * GPTQ-v2 2-bit export (train/convert_hf_to_gptq_manual.py).
+ * bdq_gptq_export_w2 = get_hf_quant_params (lines 11-75) + convert_layer_to_gptq_format (85-157) in one pass:
+ *   w [OC, IC] (T) is quantised with the converter's fp32 host arithmetic
+ *   (s = clamp(max - min, 1e-5) / 3, z = clamp(-round(min / s), 0, 3), code = clamp(round(w / s) + z, 0, 3)) and
+ *   qweight int32 [IC/16, OC]: bits [2i, 2i+2) of qweight[r, n] = code[n, 16r + i]            (lines 113-115)
+ *   qzeros  int32 [IC/G, OC/16]: bits [2i, 2i+2) of qzeros[g, c] = z[16c + i, g], NOT minus one (v2, 127-130)
+ *   scales  bf16  [IC/G, OC]: s rounded to T and then to bf16                                  (lines 64, 100)
+ * g_idx[k] = k / G is an arange the caller builds (lines 143-148).  w_bit must be 2 (line 89); group a power of two in
+ * [16, 512] with IC % group == 0; OC % 16 == 0 (line 123).  NaN weights are not supported (the reference asserts).
+ * bdq_gptq_pack_w2 is the second half alone, for callers that already hold unpacked parameters:
+ *   codes uint8 [OC, IC], zeros uint8 [OC, IC/G] -> qweight, qzeros as above.
+ */
+int bdq_gptq_export_w2(const void* w, int32_t* qweight, int32_t* qzeros, void* scales_bf16, int64_t OC, int64_t IC,
+                       int group, int w_bit, int dtype, bdq_stream_t stream);
+int bdq_gptq_pack_w2(const uint8_t* codes, const uint8_t* zeros, int32_t* qweight, int32_t* qzeros, int64_t OC,
+                     int64_t IC, int group, int w_bit, bdq_stream_t stream);
+
+/*
  * Packed 2-bit prefill GEMM: out[m, oc] = fp16( sum_k x[m,k] * fp16(scales[oc,k/G] * (code[oc,k] - zero[oc,k/G])) ),
  * fp32 accumulation in tensor memory (tcgen05.mma, TMA-fed activations, in-register dequant of the packed weights).
  * Replaces quant_matmul_v2 (quantization/triton_kernels.py:102-134) and gemm_forward_cuda (pybind.cpp:12; the

@@ -170,3 +170,14 @@ def wq_matmul(x, qweight, qzeros, qscales, G, w_bit, dequant_fp16=False):
     lib().orc_wq_matmul(_p(_f32(x)), _p(qw), _p(qz), _p(_f32(qscales)), ctypes.c_int64(B), ctypes.c_int64(IC),
                         ctypes.c_int64(OC), G, w_bit, int(dequant_fp16), _p(out))
     return torch.from_numpy(out).to(torch.float16)
+
+
+def gptq_export_w2(w, G):
+    """w [OC, IC] -> (qweight int32 [IC/16, OC], qzeros int32 [IC/G, OC/16], scales bf16 [IC/G, OC])."""
+    dt = _DT[w.dtype]
+    oc, ic = w.shape
+    qw = np.empty((ic // 16, oc), np.int32)
+    qz = np.empty((ic // G, oc // 16), np.int32)
+    sc = np.empty((ic // G, oc), np.float32)
+    lib().orc_gptq_export_w2(_p(_f32(w)), ctypes.c_int64(oc), ctypes.c_int64(ic), G, dt, _p(qw), _p(qz), _p(sc))
+    return torch.from_numpy(qw), torch.from_numpy(qz), torch.from_numpy(sc).to(torch.bfloat16)

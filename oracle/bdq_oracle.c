@@ -381,3 +381,35 @@ void orc_wq_matmul(const float *x, const int32_t *qweight, const int32_t *qzeros
     }
     free(wrow);
 }
+
+/*
+ * GPTQ-v2 2-bit export: get_hf_quant_params + convert_layer_to_gptq_format,
+ * train/convert_hf_to_gptq_manual.py:11-75 and 85-157.
+ * w [OC*IC] holds the weight values (already widened to fp32 as line 28 does); dt is the weight's own dtype, used only
+ * for the scales' trip through it (line 64) before the bf16 cast (line 100).  All arithmetic is fp32 host arithmetic.
+ * qweight [IC/16, OC]: bits 2i of [r][n] = code[n][16r+i] (113-115); qzeros [IC/G, OC/16]: bits 2i of [g][c] =
+ * z[16c+i][g] (127-130); scales [IC/G, OC] (bf16 values).
+ */
+void orc_gptq_export_w2(const float *w, int64_t OC, int64_t IC, int G, int dt, int32_t *qweight, int32_t *qzeros,
+                        float *scales) {
+    const int64_t ng = IC / G;
+    memset(qweight, 0, sizeof(int32_t) * (size_t)((IC / 16) * OC));
+    memset(qzeros, 0, sizeof(int32_t) * (size_t)(ng * (OC / 16)));
+    for (int64_t o = 0; o < OC; ++o) {
+        for (int64_t g = 0; g < ng; ++g) {
+            const float *x0 = w + o * IC + g * G;
+            float mx = x0[0], mn = x0[0];
+            for (int k = 1; k < G; ++k) { mx = fmaxf(mx, x0[k]); mn = fminf(mn, x0[k]); }
+            float s = fmaxf(mx - mn, 1e-5f) / 3.0f;                         /* line 45 */
+            float z = fminf(fmaxf(-rintf(mn / s), 0.f), 3.f);               /* line 46 */
+            uint32_t zi = (uint32_t)(int)z;
+            scales[g * OC + o] = bf16_rn(rT(s, dt));
+            ((uint32_t *)qzeros)[g * (OC / 16) + o / 16] |= zi << (2 * (o % 16));
+            for (int k = 0; k < G; ++k) {
+                float c = fminf(fmaxf(rintf(x0[k] / s) + z, 0.f), 3.f);     /* line 58 */
+                int64_t kk = g * G + k;
+                ((uint32_t *)qweight)[(kk / 16) * OC + o] |= (uint32_t)(int)c << (2 * (kk % 16));
+            }
+        }
+    }
+}

@@ -169,9 +169,42 @@ def gen_pack():
     print("pack", idx)
 
 
+def gen_gptq():
+    """train/convert_hf_to_gptq_manual.py with its `gptqmodel` import (absent here, used only by a version print) stubbed."""
+    import importlib.util
+    stub = types.ModuleType("gptqmodel")
+    stub.__version__ = "stub"
+    stub.GPTQModel = object
+    sys.modules.setdefault("gptqmodel", stub)
+    spec = importlib.util.spec_from_file_location("ref_gptq", "/root/reference/train/convert_hf_to_gptq_manual.py")
+    rg = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(rg)
+
+    out = {}
+    idx = 0
+    for dname in ["bf16", "f16", "f32"]:
+        dtype = DT[dname]
+        for kind, G, rows, cols in [("randn", 64, 32, 256), ("randn", 128, 48, 640), ("heavy", 128, 32, 1024),
+                                    ("edge", 64, 16, 256), ("pos", 32, 32, 128), ("uniform", 16, 16, 64),
+                                    ("randn", 256, 16, 512), ("randn", 512, 16, 1024)]:
+            lin = torch.nn.Linear(cols, rows, bias=(idx % 2 == 0), dtype=dtype)
+            lin.weight.data = make_inputs(kind, rows, cols, dtype, 900 + idx)
+            codes, s_t, z_t, bias = rg.get_hf_quant_params(lin, 2, True, G)
+            qw, qz, sc, g_idx, b = rg.convert_layer_to_gptq_format(codes, s_t, z_t, bias, 2, G)
+            k = f"c{idx}"
+            out[k + "_meta"] = np.array([dname, str(G)])
+            out[k + "_w"] = f32(lin.weight.data)
+            out[k + "_codes"], out[k + "_s_t"], out[k + "_z_t"] = f32(codes), f32(s_t), f32(z_t)
+            out[k + "_qweight"], out[k + "_qzeros"] = qw.numpy(), qz.numpy()
+            out[k + "_scales"], out[k + "_g_idx"] = f32(sc), g_idx.numpy()
+            idx += 1
+    np.savez_compressed(os.path.join(OUT, "gptq.npz"), **out)
+    print("gptq", idx)
+
+
 if __name__ == "__main__":
     torch.manual_seed(0)
-    which = sys.argv[1:] or ["pq", "ste", "pack", "clip"]
+    which = sys.argv[1:] or ["pq", "ste", "pack", "clip", "gptq"]
     if "pq" in which:
         gen_pq_int()
     if "ste" in which:
@@ -180,3 +213,5 @@ if __name__ == "__main__":
         gen_pack()
     if "clip" in which:
         gen_clip_autoclip()
+    if "gptq" in which:
+        gen_gptq()
