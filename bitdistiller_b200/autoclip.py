@@ -1,14 +1,19 @@
 """Drop-in for the hot-path part of the reference's quantization/autoclip.py: auto_2clip_layer (autoclip.py:13-83) and
 auto_clip_block (:86-107).  One kernel launch (bdq_autoclip) evaluates every candidate of every (output channel, group)
-pair; the reference loops 100 times over a [oc_batch, 512, ci] broadcast product.  run_clip / the CLI (HF model +
-dataset loop) are out of scope."""
+pair; the reference loops 100 times over a [oc_batch, 512, ci] broadcast product.  run_clip (autoclip.py:109-207) is the
+layer loop with the activations captured and kept ON the GPU (the reference stages every linear's input
+on the host, autoclip.py:170-173, and moves each linear to the GPU and back, :98-105); the CLI and the hub dataset loaders
+are out of scope."""
+import functools
 import gc
+from collections import defaultdict
 
 import torch
 import torch.nn as nn
 
 from . import _lib as L
-from .clip_utils import apply_clip  # noqa: F401  (autoclip.py does `from clip_utils import *`)
+from .clip_utils import (append_str_prefix, apply_clip, get_blocks, get_calib_dataset, get_named_linears,  # noqa: F401
+                         get_op_name)  # (autoclip.py does `from clip_utils import *`)
 from .quantizer import pseudo_quantize_n2f3_tensor, pseudo_quantize_tensor  # noqa: F401
 
 
@@ -68,3 +73,108 @@ def auto_clip_block(module, w_bit, q_config, input_feat):
         named_linears[name].cpu()
     gc.collect()
     return clip_list
+
+
+_SKIP = ["q_", "k_", "query", "key", "Wqkv"]
+
+
+@torch.no_grad()
+def auto_clip_block_resident(module, w_bit, q_config, input_feat):
+    """auto_clip_block for a block that already lives on the GPU with GPU-resident activations: no .cuda()/.cpu() per
+    linear, no host copies.  Same result list as auto_clip_block."""
+    clip_list = []
+    for name, lin in get_named_linears(module).items():
+        if any([_ in name for _ in _SKIP]):
+            continue
+        max_val, min_val = auto_2clip_layer(lin.weight, input_feat[name], n_bit=w_bit, q_config=q_config)
+        clip_list.append((name, max_val, min_val))
+    return clip_list
+
+
+@torch.no_grad()
+def run_clip(model, enc, w_bit, q_config, n_samples=128, seqlen=1024, datasets="pile", samples=None, device=None,
+             sharded=False):
+    """autoclip.py:109-207 with the whole loop resident on one GPU: the model is moved once (a 7B bf16 model plus the
+    [n_blocks, seqlen, hidden] activations of one layer is ~20 GB of the 180 GB), the forward hooks keep REFERENCES to the
+    linears' inputs instead of host copies, and bdq_autoclip reads the 512 sampled tokens through a row stride.  Returns the
+    reference's {"clip": [(global name, max_val, min_val), ...]} and leaves the clipped weights in the model
+    (autoclip.py:197).  `samples`: token blocks [n_blocks, seqlen] (or the list of [1, seqlen] blocks get_calib_dataset
+    returns); if None they come from get_calib_dataset(datasets, enc, n_samples, seqlen).
+    sharded=True under torch.distributed: layer i's input does not depend on the clipping of layers < i (the reference
+    forwards the block BEFORE it clips it, autoclip.py:181-197), so every rank runs the cheap forward of all blocks, searches
+    only the layers it owns and one all-gather completes the list (sharded.gather_clip_cache); the weights of all layers
+    are then clipped from the gathered list, so every rank ends with the same model."""
+    if samples is None:
+        print(f"Using {datasets} dataset to do calibation")
+        samples = get_calib_dataset(datasets=datasets, tokenizer=enc, n_samples=n_samples, block_size=seqlen)
+    if isinstance(samples, (list, tuple)):
+        samples = torch.cat(list(samples), dim=0)
+    dev = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
+    layers = get_blocks(model)
+    model.to(dev)
+
+    inps, layer_kwargs = [], {}
+
+    class Catcher(nn.Module):
+        def __init__(self, module):
+            super().__init__()
+            self.module = module
+
+        def __getattr__(self, name):            # newer transformers read attributes (attention_type) off the layer
+            try:
+                return super().__getattr__(name)
+            except AttributeError:
+                return getattr(self.module, name)
+
+        def forward(self, inp, **kwargs):
+            inps.append(inp)
+            layer_kwargs.update(kwargs)
+            raise ValueError  # early exit to break later inference
+
+    layers[0] = Catcher(layers[0])
+    try:
+        model(samples.to(dev))
+    except ValueError:
+        pass
+    layers[0] = layers[0].module
+    inps = inps[0]
+
+    if sharded:
+        import torch.distributed as dist
+
+        from .sharded import gather_clip_cache, owned_layers
+        mine = set(owned_layers(len(layers), dist.get_rank(), dist.get_world_size()))
+    else:
+        mine = set(range(len(layers)))
+
+    clip_results = {"clip": []}
+    for i in range(len(layers)):
+        layer = layers[i]
+        named_linears = get_named_linears(layer)
+        input_feat = defaultdict(list)
+        handles = []
+        if i in mine:
+            def cache_input_hook(m, x, y, name, feat_dict):
+                feat_dict[name].append(x[0].detach())     # stays on the GPU; q/k/v and gate/up share one tensor
+            for name in named_linears:
+                if any([_ in name for _ in _SKIP]):
+                    continue
+                handles.append(named_linears[name].register_forward_hook(
+                    functools.partial(cache_input_hook, name=name, feat_dict=input_feat)))
+        out = layer(inps, **layer_kwargs)
+        inps = out[0] if isinstance(out, (tuple, list)) else out
+        for h in handles:
+            h.remove()
+        if i not in mine:
+            continue
+        input_feat = {k: (v[0] if len(v) == 1 else torch.cat(v, dim=0)) for k, v in input_feat.items()}
+        clip_list = auto_clip_block_resident(layer, w_bit=w_bit, q_config=q_config, input_feat=input_feat)
+        if not sharded:
+            apply_clip(layer, clip_list)
+        clip_results["clip"] += append_str_prefix(clip_list, get_op_name(model, layer) + ".")
+        del input_feat
+    if sharded:
+        wdtype = next(layers[0].parameters()).dtype
+        clip_results["clip"] = gather_clip_cache(clip_results["clip"], dtype=wdtype, device=dev)
+        apply_clip(model, clip_results)
+    return clip_results

@@ -24,6 +24,53 @@ def get_op_name(module, op):
     raise ValueError(f"Cannot find op {op} in module {module}")
 
 
+def append_str_prefix(x, prefix):
+    """clip_utils.py:257-265: prefix every string of a nested list / tuple structure."""
+    if isinstance(x, str):
+        return prefix + x
+    elif isinstance(x, tuple):
+        return tuple([append_str_prefix(y, prefix) for y in x])
+    elif isinstance(x, list):
+        return [append_str_prefix(y, prefix) for y in x]
+    else:
+        return x
+
+
+def get_blocks(model):
+    from .pre_quant import get_blocks as _gb
+    return _gb(model)
+
+
+def get_calib_dataset(datasets="pileval", tokenizer=None, n_samples=128, block_size=1024):
+    """clip_utils.py:32-48 dispatches on hub dataset names ("pile", "gsm8k", "code", ...) that need network access or the
+    authors' local paths: that loader is outside the hot path (out of scope).  Here `datasets` may be a local
+    text / jsonl file (one sample per line, jsonl key "text"); samples are tokenised, concatenated and cut into
+    [1, block_size] blocks exactly like the reference loaders (clip_utils.py:72-77)."""
+    import json
+    import os
+    if not (isinstance(datasets, str) and os.path.exists(datasets)):
+        raise NotImplementedError(
+            f"calibration corpus {datasets!r}: hub loaders are out of scope here; pass a local text/jsonl path, or give "
+            "run_clip the token blocks directly (samples=...)")
+    samples, n_run = [], 0
+    with open(datasets) as f:
+        for line in f:
+            line = line.strip()
+            if datasets.endswith(".jsonl") and line:
+                line = json.loads(line)["text"].strip()
+            enc = tokenizer.encode(line)
+            if len(enc) > 512 or len(enc) == 0:
+                continue
+            samples.append(torch.tensor([enc]))
+            n_run += 1
+            if n_run == n_samples:
+                break
+    cat = torch.cat(samples, dim=1)
+    n_split = cat.shape[1] // block_size
+    print(f" * Split into {n_split} blocks")
+    return [cat[:, i * block_size:(i + 1) * block_size] for i in range(n_split)]
+
+
 def clip_weight_(w, min_val, max_val):
     """In-place w = clamp(w.reshape(co, n_g, G), min_val, max_val) through bdq_apply_clip."""
     L.require_cuda(w, min_val, max_val)

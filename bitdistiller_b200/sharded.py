@@ -222,3 +222,156 @@ def tp_gemm_fused(x, shard, rows, group_size=128):
                                     L.i64(ic), L.i64(ocl), int(group_size), L.i64(rows.OC), len(peers), peerp,
                                     L.stream_ptr(x.device))
     L.check(rc, "bdq_gemm_w2_tp")
+
+
+# ------------------------------------------------------------------------------------------------- quantise, then gather
+def payload_layout(rows, cols, group_size, world, multiple=16):
+    """Byte layout of the gathered int2 payload of a [rows, cols] weight split on dim 0 by `row_shard`: per rank
+    (row0, row1, codes byte offset, codes bytes, scale/zero byte offset, scale/zero bytes).  Codes take 2 bits per weight,
+    every group one (scale, zero) pair of 2-byte values; shards are whole rows, hence whole groups and whole 32-element
+    code words, so the concatenation of the rank payloads IS the payload of the full weight."""
+    if cols % group_size != 0 or group_size % 32 != 0:
+        raise ValueError(f"cols={cols} must be a multiple of group_size={group_size}, itself a multiple of 32")
+    out = []
+    for r in range(world):
+        r0, r1 = row_shard(rows, r, world, multiple if world > 1 else 1)
+        out.append((r0, r1, r0 * cols // 4, (r1 - r0) * cols // 4, r0 * (cols // group_size) * 4,
+                    (r1 - r0) * (cols // group_size) * 4))
+    return out
+
+
+def gather_payload(local_codes, local_sz, layout, group=None):
+    """Collective transport of the payload (the path without peer-mapped memory; also what the gloo tests run): uint8
+    tensors of this rank's slot -> the full (codes, sz) byte tensors on every rank."""
+    world = len(layout)
+    if world == 1 or not (dist.is_available() and dist.is_initialized()):
+        return local_codes, local_sz
+    dev = local_codes.device
+    cmax, smax = max(l[3] for l in layout), max(l[5] for l in layout)
+    send = torch.zeros(cmax + smax, dtype=torch.uint8, device=dev)       # ragged shards: pad every slot to the largest
+    send[: local_codes.numel()] = local_codes
+    send[cmax: cmax + local_sz.numel()] = local_sz
+    recv = torch.empty(world * (cmax + smax), dtype=torch.uint8, device=dev)
+    dist.all_gather_into_tensor(recv, send, group=group)
+    recv = recv.view(world, cmax + smax)
+    return (torch.cat([recv[r, : l[3]] for r, l in enumerate(layout)]),
+            torch.cat([recv[r, cmax: cmax + l[5]] for r, l in enumerate(layout)]))
+
+
+class ShardGather:
+    """Quantise-before-all-gather of ONE int2 QLinear weight [rows, cols] held as dim-0 shards (FSDP2 layout):
+    `forward(w_shard)` returns the fake-quantised FULL weight on every rank, bit-equal to
+    SteInt2AsymQuantizer(group)(all_gather(w_shard)) (quantization/quantizer.py:153-182), moving 0.28 B/weight over NVLink
+    instead of 2.  With `symmetric=True` the encode kernel stores its payload straight into every rank's gather buffer
+    (torch symmetric memory, bdq_int2_shard_encode's peer destinations) and only a barrier separates it from the decode;
+    otherwise the payload goes through torch.distributed all_gather.  `backward(w_shard, g_full)`: reduce-scatter of the
+    gradient w.r.t. the quantised weight, then the fused STE backward on the shard (the STE backward is linear in the
+    incoming gradient and group-local, so it commutes with the sum over ranks)."""
+
+    def __init__(self, rows, cols, group_size, dtype, device, group=None, symmetric=True, round_mode=None):
+        from . import _lib as L
+        self.rows, self.cols, self.group_size, self.dtype, self.device = rows, cols, group_size, dtype, torch.device(device)
+        self.pg = group
+        on = dist.is_available() and dist.is_initialized()
+        self.rank = dist.get_rank(group) if on else 0
+        self.world = dist.get_world_size(group) if on else 1
+        self.layout = payload_layout(rows, cols, group_size, self.world)
+        self.round_mode = L.ROUND_HALF_AWAY if round_mode is None else round_mode
+        ncode = rows * cols // 4
+        nsz = rows * (cols // group_size) * 4
+        self.symmetric = bool(symmetric) and self.world > 1
+        if self.symmetric:
+            import torch.distributed._symmetric_memory as symm_mem
+            self.buf = symm_mem.empty(ncode + nsz, dtype=torch.uint8, device=self.device)
+            self.hdl = symm_mem.rendezvous(self.buf, self.pg if self.pg is not None else dist.group.WORLD)
+            self.ptrs = [int(p) for p in self.hdl.buffer_ptrs]
+        else:
+            self.buf = torch.empty(ncode + nsz, dtype=torch.uint8, device=self.device)
+            self.ptrs = [self.buf.data_ptr()]
+        self.codes = self.buf[:ncode]
+        self.sz = self.buf[ncode:]
+        self._sz_off = ncode
+
+    def _encode(self, w_shard):
+        import ctypes
+
+        from . import _lib as L
+        r0, r1, coff, cbytes, soff, sbytes = self.layout[self.rank]
+        assert w_shard.shape == (r1 - r0, self.cols) and w_shard.dtype == self.dtype
+        L.require_cuda(w_shard)
+        w = w_shard.detach().contiguous()
+        base = self.buf.data_ptr()
+        peers = [p for i, p in enumerate(self.ptrs) if i != self.rank] if self.symmetric else []
+        pc = (ctypes.c_void_p * max(len(peers), 1))(*[p + coff for p in peers])
+        ps = (ctypes.c_void_p * max(len(peers), 1))(*[p + self._sz_off + soff for p in peers])
+        with torch.cuda.device(self.device):
+            rc = L.lib().bdq_int2_shard_encode(L.ptr(w), ctypes.c_void_p(base + coff), ctypes.c_void_p(base + self._sz_off + soff),
+                                               L.i64(w.numel()), int(self.group_size), L.dtype_code(w), int(self.round_mode),
+                                               L.semantics(), len(peers), pc, ps, L.stream_ptr(self.device))
+        L.check(rc, "bdq_int2_shard_encode")
+
+    def _decode(self, codes, sz):
+        from . import _lib as L
+        dq = torch.empty((self.rows, self.cols), dtype=self.dtype, device=self.device)
+        with torch.cuda.device(self.device):
+            rc = L.lib().bdq_int2_shard_decode(L.ptr(codes), L.ptr(sz), L.ptr(dq), L.i64(dq.numel()), int(self.group_size),
+                                               L.dtype_code(dq), L.stream_ptr(self.device))
+        L.check(rc, "bdq_int2_shard_decode")
+        return dq
+
+    @torch.no_grad()
+    def forward(self, w_shard):
+        if self.symmetric:
+            self.hdl.barrier(channel=0)          # every rank is done reading the previous payload
+            self._encode(w_shard)
+            self.hdl.barrier(channel=0)          # every slot of this rank's buffer has been written
+            return self._decode(self.codes, self.sz)
+        self._encode(w_shard)
+        if self.world == 1:
+            return self._decode(self.codes, self.sz)
+        _, _, coff, cbytes, soff, sbytes = self.layout[self.rank]
+        codes, sz = gather_payload(self.codes[coff:coff + cbytes], self.sz[soff:soff + sbytes], self.layout, self.pg)
+        return self._decode(codes, sz)
+
+    @torch.no_grad()
+    def backward(self, w_shard, g_full, average=False):
+        from . import _lib as L
+        r0, r1 = self.layout[self.rank][:2]
+        g_full = g_full.to(self.dtype).contiguous()
+        if self.world > 1:
+            sizes = [l[1] - l[0] for l in self.layout]
+            if len(set(sizes)) == 1:
+                g = torch.empty((r1 - r0, self.cols), dtype=self.dtype, device=g_full.device)
+                dist.reduce_scatter_tensor(g, g_full, op=dist.ReduceOp.SUM, group=self.pg)
+            else:
+                dist.all_reduce(g_full, op=dist.ReduceOp.SUM, group=self.pg)
+                g = g_full[r0:r1].contiguous()
+            if average:
+                g /= self.world
+        else:
+            g = g_full
+        w = w_shard.detach().contiguous()
+        gw = torch.empty_like(w)
+        with torch.cuda.device(w.device):
+            rc = L.lib().bdq_int_ste_bwd(L.ptr(w), L.ptr(g), L.ptr(gw), L.i64(w.numel()), int(self.group_size), 2,
+                                         L.dtype_code(w), L.semantics(), L.stream_ptr(w.device))
+        L.check(rc, "bdq_int_ste_bwd")
+        return gw
+
+
+class _ShardGatherFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, w_shard, gatherer, average):
+        ctx.gatherer, ctx.average = gatherer, average
+        ctx.save_for_backward(w_shard)
+        return gatherer.forward(w_shard)
+
+    @staticmethod
+    def backward(ctx, g_full):
+        (w_shard,) = ctx.saved_tensors
+        return ctx.gatherer.backward(w_shard, g_full, ctx.average), None, None
+
+
+def quantized_all_gather(w_shard, gatherer, average=False):
+    """Autograd entry: shard parameter -> fake-quantised full weight (see ShardGather)."""
+    return _ShardGatherFn.apply(w_shard, gatherer, average)

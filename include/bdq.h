@@ -210,6 +210,26 @@ int bdq_gemm_w2_tp(const void* x, const int32_t* qweight, const void* scales, co
                    int64_t IC, int64_t OC_local, int group, int64_t ldo, int n_peer, void* const* peer_out, bdq_stream_t stream);
 
 /*
+ * Quantise-before-all-gather for dim-0 (FSDP2-style) shards of a QLinear weight.  The reference
+ * gathers the bf16 shards and fake-quantises the full weight on every rank (QLinear.forward, quantization/qlinear.py:63-78,
+ * with SteInt2AsymQuantizer, quantizer.py:153-182); groups lie along the last dimension, so the owner of a shard can
+ * quantise it once and ship 2-bit codes + one (scale, zero) pair per group: 0.28 B/weight instead of 2.
+ *   bdq_int2_shard_encode: w [n_elem] (bf16 / fp16) -> codes [n_elem/4 bytes], sz [n_elem/group] pairs of T (scale, zero).
+ *     The payload is stored to `codes`/`sz` AND to the n_peer (<= 7) peer-mapped destinations peer_codes[i]/peer_sz[i]
+ *     (NVLink addresses of this rank's slot in every peer's gather buffer, e.g. torch symmetric memory): the all-gather is
+ *     the kernel's store phase.  The caller puts a cross-rank barrier between the encode launches and the decode.
+ *     round_mode: BDQ_ROUND_HALF_AWAY = SteInt2AsymQuantizer, BDQ_ROUND_HALF_EVEN = pseudo_quantize_tensor.
+ *   bdq_int2_shard_decode: dq = rT((code - zero) * scale), the last two operations of quantizer.py:177 -- bit-equal to
+ *     bdq_int_fakequant_fwd(bits 2) of the same weights.
+ * Code layout: one uint2 per 32 consecutive elements, one 32-bit word per 16; element j of the 16 sits at bits
+ * [16*(j%2) + 2*(j/2), +2).  group in {32, 64, 128}; w and dq 32-byte aligned, codes 8-byte, sz 4-byte.
+ */
+int bdq_int2_shard_encode(const void* w, void* codes, void* sz, int64_t n_elem, int group, int dtype, int round_mode,
+                          int sem, int n_peer, void* const* peer_codes, void* const* peer_sz, bdq_stream_t stream);
+int bdq_int2_shard_decode(const void* codes, const void* sz, void* dq, int64_t n_elem, int group, int dtype,
+                          bdq_stream_t stream);
+
+/*
  * Two-sided clip-ratio grid search = auto_2clip_layer (quantization/autoclip.py:13-83), all candidates of all
  * (output channel, group) pairs in one launch.  w [co, ci] (T, row-major); x = the calibration activations
  * [n_tok, ci] of the same dtype with a row stride of x_row_stride elements (the reference's token sub-sampling

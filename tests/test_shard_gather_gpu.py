@@ -1,0 +1,137 @@
+"""GPU parity tests of the quantise-before-all-gather path (bdq_int2_shard_encode / _decode, sharded.ShardGather).
+
+Bar: the 2-bit codes, scales and zeros of the payload are bit-exact against the oracle (oracle/bdq_oracle.c, pinned by the
+reference-generated golden vectors), and decode(encode(w)) is bit-equal to the fake-quantiser forward
+(SteInt2AsymQuantizer, quantization/quantizer.py:153-182 / pseudo_quantize_tensor, :25-69) on the same weights."""
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from _util import DT, bits_equal, load_cases, make_weight, t
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(autouse=True)
+def _cpu_semantics(monkeypatch):
+    monkeypatch.setenv("BDQ_SEMANTICS", "cpu")
+
+
+def dev():
+    return torch.device("cuda:0")
+
+
+def unpack_codes(code_bytes, n):
+    """Wire format of include/bdq.h: one 32-bit word per 16 elements, element j at bits [16*(j%2) + 2*(j//2), +2)."""
+    words = code_bytes.cpu().numpy().view(np.uint32).astype(np.uint64)
+    j = np.arange(16)
+    shift = (16 * (j % 2) + 2 * (j // 2)).astype(np.uint64)
+    return ((words[:, None] >> shift[None, :]) & 3).astype(np.uint8).reshape(-1)[:n]
+
+
+def roundtrip(w, G, round_mode):
+    from bitdistiller_b200 import sharded as S
+    g = S.ShardGather(w.shape[0], w.shape[1], G, w.dtype, w.device, symmetric=False, round_mode=round_mode)
+    dq = g.forward(w)
+    torch.cuda.synchronize()
+    sz = g.sz.view(w.dtype).view(-1, 2)
+    return dq, unpack_codes(g.codes, w.numel()), sz[:, 0].clone(), sz[:, 1].clone()
+
+
+@pytest.mark.parametrize("dname", ["bf16", "f16"])
+@pytest.mark.parametrize("G", [32, 64, 128])
+@pytest.mark.parametrize("round_mode", [0, 1])
+def test_payload_matches_oracle_and_fake_quantiser(dname, G, round_mode):
+    from bitdistiller_b200.quantizer import int_fakequant
+    dt = DT[dname]
+    for kind, seed in [("randn", 1), ("uniform", 2), ("heavy", 3)]:
+        w = make_weight(kind, 48, 1024, dt, seed)
+        w[3, :G] = 0.25                      # constant group: max - min clamps to 1e-5
+        w[5, G:2 * G] = 0.0
+        w[7, :G] = w[7, :G].abs()            # all-positive group: zero point 0
+        w[9, :G] = -w[9, :G].abs()           # all-negative group: zero point 3
+        wd = w.to(dev())
+        dq, codes, s, z = roundtrip(wd, G, round_mode)
+        o = oracle.int_fakequant(w, G, 2, round_mode=round_mode)
+        assert np.array_equal(codes, o["codes"].numpy().reshape(-1)), (kind, dname, G)
+        assert bits_equal(s.cpu(), o["scales"].reshape(-1)) and bits_equal(z.cpu(), o["zeros"].reshape(-1))
+        assert bits_equal(dq.cpu(), o["dq"])
+        ref, _, _, _ = int_fakequant(wd, 2, G, round_mode)
+        assert torch.equal(dq.view(torch.int16), ref.view(torch.int16)), (kind, dname, G)
+
+
+def test_golden_cases_round_trip():
+    """The committed reference-generated vectors of pseudo_quantize_tensor (2-bit, 16-bit dtypes)."""
+    n = 0
+    for meta, c in load_cases("pq_int"):
+        dname, n_bit, G = meta[0], int(meta[2]), int(meta[3])
+        if n_bit != 2 or dname == "f32" or G not in (32, 64, 128):
+            continue
+        dt = DT[dname]
+        w = t(c["w"], dt).to(dev())
+        dq, _, s, z = roundtrip(w, G, 0)
+        assert bits_equal(dq.cpu(), t(c["dq"], dt)), meta
+        assert bits_equal(s.cpu(), t(c["s"], dt).reshape(-1)) and bits_equal(z.cpu(), t(c["z"], dt).reshape(-1)), meta
+        n += 1
+    assert n == 20
+
+
+def test_nan_inf_and_slow_path_groups():
+    from bitdistiller_b200.quantizer import int_fakequant
+    w = make_weight("randn", 16, 512, torch.bfloat16, 7)
+    w[0, 5] = float("nan")
+    w[1, 130] = float("inf")
+    w[2, :128] *= 1e30                       # huge range: quotients leave the bracketing window -> op-by-op path
+    w[3, :128] *= 1e-30
+    w[4, 0:128] = 3e38
+    wd = w.to(dev())
+    dq, codes, s, z = roundtrip(wd, 128, 1)
+    ref, _, _, _ = int_fakequant(wd, 2, 128, 1)
+    assert bits_equal(dq.cpu(), ref.cpu())
+    fin = torch.isfinite(ref.reshape(-1, 128)).all(1).cpu()
+    o = oracle.int_fakequant(w, 128, 2, round_mode=1)
+    keep = fin.repeat_interleave(128).numpy()
+    assert np.array_equal(codes[keep], o["codes"].numpy().reshape(-1)[keep])
+
+
+def test_large_layer_bit_equal_and_linear_layout():
+    """Llama-2-7B sized tensor: decode(encode(w)) == forward(w); the payload of row shards concatenates to the payload of
+    the whole weight (what makes the gather a plain concatenation)."""
+    from bitdistiller_b200 import sharded as S
+    from bitdistiller_b200.quantizer import SteInt2AsymQuantizer
+    w = (torch.randn(11008, 4096, device=dev()) * 0.02).bfloat16()
+    full = S.ShardGather(11008, 4096, 128, torch.bfloat16, dev(), symmetric=False)
+    dq = full.forward(w)
+    assert torch.equal(dq.view(torch.int16), SteInt2AsymQuantizer(128)(w).view(torch.int16))
+    lay = S.payload_layout(11008, 4096, 128, 8)
+    for r in (0, 3, 7):
+        r0, r1, coff, cb, soff, sb = lay[r]
+        part = S.ShardGather(r1 - r0, 4096, 128, torch.bfloat16, dev(), symmetric=False)
+        part.forward(w[r0:r1])
+        assert torch.equal(part.codes, full.codes[coff:coff + cb]) and torch.equal(part.sz, full.sz[soff:soff + sb])
+
+
+def test_autograd_matches_ste_quantizer():
+    from bitdistiller_b200 import sharded as S
+    from bitdistiller_b200.quantizer import SteInt2AsymQuantizer
+    w = (torch.randn(64, 512, device=dev()) * 0.02).bfloat16()
+    gy = torch.randn(64, 512, device=dev()).bfloat16()
+    a = w.clone().requires_grad_(True)
+    b = w.clone().requires_grad_(True)
+    g = S.ShardGather(64, 512, 128, torch.bfloat16, dev(), symmetric=False)
+    S.quantized_all_gather(a, g).backward(gy)
+    SteInt2AsymQuantizer(128)(b).backward(gy)
+    assert torch.equal(a.grad.view(torch.int16), b.grad.view(torch.int16))
+
+
+def test_errors():
+    from bitdistiller_b200 import _lib as L
+    lib = L.lib()
+    i64 = L.i64
+    assert lib.bdq_int2_shard_encode(None, None, None, i64(100), 128, 1, 1, 0, 0, None, None, None) == -1
+    assert lib.bdq_int2_shard_encode(None, None, None, i64(128), 128, 0, 1, 0, 0, None, None, None) == -2
+    assert lib.bdq_int2_shard_encode(None, None, None, i64(96), 48, 1, 1, 0, 0, None, None, None) == -5
+    assert lib.bdq_int2_shard_encode(None, None, None, i64(128), 128, 1, 1, 0, 8, None, None, None) == -1
+    assert lib.bdq_int2_shard_decode(None, None, None, i64(0), 128, 1, None) == 0
+    assert lib.bdq_int2_shard_decode(None, None, None, i64(128), 128, 1, None) == -1

@@ -68,6 +68,13 @@ def _worker(rank, world, port, q):
             r0, r1 = S.row_shard(64, rank, world)
             got = S.all_gather_cols(whole[:, r0:r1].contiguous())
             ok = ok and torch.equal(got, whole)
+        # quantise-then-gather payload transport: the concatenation of the rank slots is the full payload
+        lay = S.payload_layout(48, 256, 128, world)
+        allc = torch.arange(48 * 256 // 4, dtype=torch.int64).remainder(251).to(torch.uint8)
+        alls = torch.arange(48 * 2 * 4, dtype=torch.int64).remainder(241).to(torch.uint8)
+        _, _, coff, cb, soff, sb = lay[rank]
+        gc_, gs_ = S.gather_payload(allc[coff:coff + cb], alls[soff:soff + sb], lay)
+        ok = ok and torch.equal(gc_, allc) and torch.equal(gs_, alls)
         q.put((rank, bool(ok)))
     finally:
         dist.destroy_process_group()
@@ -84,3 +91,16 @@ def test_sharded_gathers_world2_gloo():
     for p in ps:
         p.join(timeout=60)
     assert res == [(0, True), (1, True)]
+
+
+def test_payload_layout_is_a_partition():
+    for rows, cols, G, world in [(4096, 4096, 128, 8), (11008, 4096, 128, 8), (4096, 11008, 128, 8), (48, 256, 64, 2), (16, 64, 32, 3)]:
+        lay = S.payload_layout(rows, cols, G, world)
+        assert lay[0][0] == 0 and lay[-1][1] == rows and lay[0][2] == 0 and lay[0][4] == 0
+        for a, b in zip(lay, lay[1:]):
+            assert a[1] == b[0] and a[2] + a[3] == b[2] and a[4] + a[5] == b[4]
+        assert lay[-1][2] + lay[-1][3] == rows * cols // 4                 # 2 bits per weight
+        assert lay[-1][4] + lay[-1][5] == rows * (cols // G) * 4           # (scale, zero) 2 x 2 bytes per group
+        assert all(l[2] % 8 == 0 and l[4] % 4 == 0 for l in lay)           # kernel alignment of every slot
+    with pytest.raises(ValueError):
+        S.payload_layout(16, 100, 128, 2)
