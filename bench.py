@@ -340,6 +340,18 @@ def secondary_metrics(torch, dev, peak):
     out["gemv_int2_kernel_streaming"] = {"shape": [big["OC"], big["IC"]], "mb": big["MB"], "us_per_launch": big["us_per_launch"],
                                          "gbs": big["gbs"], "frac_of_hbm_peak": big["frac_of_hbm_peak"],
                                          "what": "the same batch-1 kernel on one lm_head-sized launch (cold, distinct copies)"}
+    try:
+        from tools import bench_shard_gather
+        sg = bench_shard_gather.single(dev)
+        out["int2_shard_gather_llama2_7b_layer"] = {
+            "what": "SURVEY 8f N4, quantise-before-all-gather kernels on one decoder layer's flat bf16 buffer (202.4 M weights) "
+                    "per launch: encode = 2 B read + 0.28 B payload written per weight, decode = the reverse; decode(encode(w)) "
+                    "is checked bit-equal to the fake-quantiser in this run",
+            "encode_gbs": sg["encode"]["gbs"], "encode_frac_of_hbm_peak": sg["encode"]["gbs"] / peak,
+            "decode_gbs": sg["decode"]["gbs"], "decode_frac_of_hbm_peak": sg["decode"]["gbs"] / peak,
+            "payload_bytes_per_weight": sg["payload_bytes_per_weight"]}
+    except Exception as e:
+        out["int2_shard_gather_llama2_7b_layer"] = {"error": f"{type(e).__name__}: {e}"[:300]}
     return out
 
 

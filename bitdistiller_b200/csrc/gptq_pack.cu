@@ -10,6 +10,7 @@
 //
 // Arithmetic is the reference's fp32 CPU arithmetic (the converter upcasts the weight and runs on the host):
 // s = clamp(max - min, 1e-5) / 3 (IEEE division), z = clamp(-rne(min / s), 0, 3), code = clamp(rne(w / s) + z, 0, 3).
+#include "fakequant_thr.cuh"
 #include "fq_int_elem.cuh"
 
 namespace bdq {
@@ -36,6 +37,36 @@ __device__ __forceinline__ void load16(const void* w, int64_t idx, bool vec_ok, 
     }
 }
 
+// ---- threshold form for 16-bit weights (the converter upcasts them and computes in fp32): for one group the code
+// c(x) = clamp(rne(x / s) + z, 0, 3) is a monotone step function of the T value x, so it is described by the three
+// smallest T values T_k with rne(fdiv(x, s)) >= k - z.  Each is found by evaluating that exact fp32 predicate on the 5 T
+// values around rT((k - z - 0.5) s) and accepted only if it flips inside the window (else the group goes op by op).
+template <int DT>
+__device__ __forceinline__ float gptq_threshold(float n, float s, bool& ok) {
+    const float xc = rT<DT>((n - 0.5f) * s);
+    uint32_t pm = 0;
+#pragma unroll
+    for (int j = 0; j < 5; ++j) pm |= (rintf(__fdiv_rn(t_step<DT>(xc, j - 2), s)) >= n ? 1u : 0u) << j;
+    const int i = __ffs(pm) - 1;
+    ok = (i >= 1) && (pm == ((0x1fu << i) & 0x1fu));
+    return t_step<DT>(xc, i - 2);
+}
+
+template <int DT>
+struct GqMagic;
+template <>
+struct GqMagic<kBF16> { static constexpr float v = 128.f; static constexpr uint32_t bits2 = 0x43004300u; };
+template <>
+struct GqMagic<kF16> { static constexpr float v = 1024.f; static constexpr uint32_t bits2 = 0x64006400u; };
+
+// 8 two-bit fields at 2-bit pitch (16 bits) -> 4-bit pitch
+__device__ __forceinline__ uint32_t spread2(uint32_t x) {
+    x = (x | (x << 8)) & 0x00FF00FFu;
+    x = (x | (x << 4)) & 0x0F0F0F0Fu;
+    x = (x | (x << 2)) & 0x33333333u;
+    return x;
+}
+
 // MODE 0: quantise `w` (T) here.  MODE 1: `w` holds uint8 codes [OC, IC] and `zin` uint8 zeros [OC, IC/G]
 // (the two-step API, convert_layer_to_gptq_format on already unpacked parameters); scales are not touched.
 template <int DT, int MODE>
@@ -53,7 +84,8 @@ __global__ void __launch_bounds__(kGqWarps * 32) gptq_pack_w2_kernel(const void*
     const int lpg = group >> 4;                      // lanes per group (power of two, 1..32)
     const int64_t k = k0 + 16 * lane;
     const bool k_ok = k < IC;
-    const int64_t ng = IC / group;
+    const int lg = 31 - __clz(group);             // group is a power of two (checked by the host): shifts, not divisions
+    const int64_t ng = IC >> lg;
 
 #pragma unroll 1
     for (int j = 0; j < kGqTileO / kGqWarps; ++j) {
@@ -62,28 +94,99 @@ __global__ void __launch_bounds__(kGqWarps * 32) gptq_pack_w2_kernel(const void*
         const bool ok = k_ok && o < OC;              // warp-uniform in o; whole groups are in or out in k
         uint32_t word = 0;
         if constexpr (MODE == 0) {
-            float f[16];
-            if (ok) load16<DT>(w, o * IC + k, vec_ok, f);
-            else {
+            IntQ p;
+            bool done = false;
+            if constexpr (DT != kF32) {
+                if (vec_ok) {                        // warp-uniform
+                    using P = P2<DT>;
+                    using h2 = typename P::h2;
+                    U8 raw;
+                    if (ok) raw = ldg256(reinterpret_cast<const uint8_t*>(w) + (o * IC + k) * 2);
+                    else {
 #pragma unroll
-                for (int i = 0; i < 16; ++i) f[i] = 0.f;
+                        for (int i = 0; i < 8; ++i) raw.r[i] = 0u;
+                    }
+                    float mx, mn;
+                    vec_minmax16<DT>(raw, mx, mn);
+                    for (int d = lpg >> 1; d > 0; d >>= 1) {
+                        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, d));
+                        mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, d));
+                    }
+                    p = int_group_params<kF32>(mx, mn, 3.f, BDQ_SEM_CPU);
+                    const int lig = lane & (lpg - 1), gbase = lane & ~(lpg - 1);
+                    // every lane evaluates ONE threshold per round (k = lig + r * lpg): no divergence between the lanes of a
+                    // group; one round when the group spans >= 4 lanes (G >= 64)
+                    float tl0 = 0.f, tl1 = 0.f, tl2 = 0.f;
+                    bool tok = fmaxf(fabsf(mx), fabsf(mn)) < 1e30f && p.s > 1e-30f;
+                    const int rounds = lpg >= 4 ? 1 : (lpg == 2 ? 2 : 3);
+#pragma unroll 1
+                    for (int r = 0; r < rounds; ++r) {
+                        const int kk = lig + r * lpg;
+                        bool o1 = true;
+                        float tv = 0.f;
+                        if (kk < 3) tv = gptq_threshold<DT>((float)(kk + 1) - p.z, p.s, o1);
+                        tok = tok && o1;
+                        if (r == 0) tl0 = tv; else if (r == 1) tl1 = tv; else tl2 = tv;
+                    }
+                    const uint32_t okm = __ballot_sync(0xffffffffu, tok);
+                    const uint32_t gm = (lpg == 32 ? 0xffffffffu : ((1u << lpg) - 1u)) << gbase;
+                    h2 t2[3];
+#pragma unroll
+                    for (int kk = 0; kk < 3; ++kk) {
+                        const int r = lpg >= 4 ? 0 : (kk >> (lg - 4));
+                        const float src = r == 0 ? tl0 : (r == 1 ? tl1 : tl2);
+                        t2[kk] = P::dup(__shfl_sync(0xffffffffu, src, gbase + (kk & (lpg - 1))));
+                    }
+                    if ((okm & gm) == gm) {
+                        const h2 magic = P::dup(GqMagic<DT>::v);
+                        uint32_t acc = 0u;
+#pragma unroll
+                        for (int i = 7; i >= 0; --i) {
+                            const h2 x2 = P::from_bits(raw.r[i]);
+                            h2 c2 = __hadd2(__hge2(x2, t2[0]), magic);
+                            c2 = __hadd2(c2, __hge2(x2, t2[1]));
+                            c2 = __hadd2(c2, __hge2(x2, t2[2]));
+                            acc = acc * 4u + P::bits(c2);
+                        }
+                        acc -= GqMagic<DT>::bits2 * 21845u;              // even elements in the low half, odd in the high half
+                        word = spread2(acc & 0xFFFFu) | (spread2(acc >> 16) << 2);
+                    } else {
+                        float f[16];
+                        unpack<DT>(raw, f);
+#pragma unroll 1
+                        for (int i = 0; i < 16; ++i) {
+                            float qu;
+                            const float c = quant_code<kF32, BDQ_ROUND_HALF_EVEN>(f[i], p, 3.f, qu);
+                            word |= (uint32_t)(int)c << (2 * i);
+                        }
+                    }
+                    done = true;
+                }
             }
-            float mx = f[0], mn = f[0];
+            if (!done) {
+                float f[16];
+                if (ok) load16<DT>(w, o * IC + k, vec_ok, f);
+                else {
 #pragma unroll
-            for (int i = 1; i < 16; ++i) { mx = fmaxf(mx, f[i]); mn = fminf(mn, f[i]); }
-            for (int d = lpg >> 1; d > 0; d >>= 1) {
-                mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, d));
-                mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, d));
-            }
-            const IntQ p = int_group_params<kF32>(mx, mn, 3.f, BDQ_SEM_CPU);
+                    for (int i = 0; i < 16; ++i) f[i] = 0.f;
+                }
+                float mx = f[0], mn = f[0];
 #pragma unroll
-            for (int i = 0; i < 16; ++i) {
-                float qu;
-                const float c = quant_code<kF32, BDQ_ROUND_HALF_EVEN>(f[i], p, 3.f, qu);
-                word |= (uint32_t)(int)c << (2 * i);
+                for (int i = 1; i < 16; ++i) { mx = fmaxf(mx, f[i]); mn = fminf(mn, f[i]); }
+                for (int d = lpg >> 1; d > 0; d >>= 1) {
+                    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, d));
+                    mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, d));
+                }
+                p = int_group_params<kF32>(mx, mn, 3.f, BDQ_SEM_CPU);
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    float qu;
+                    const float c = quant_code<kF32, BDQ_ROUND_HALF_EVEN>(f[i], p, 3.f, qu);
+                    word |= (uint32_t)(int)c << (2 * i);
+                }
             }
             if (ok && (lane & (lpg - 1)) == 0) {
-                const int gl = lane / lpg;
+                const int gl = lane >> (lg - 4);
                 // scales leave get_hf_quant_params in the weight's dtype (line 64) and are then cast to bf16 (line 100)
                 s_scale[gl][ol] = rT<DT>(p.s);
                 s_zero[gl][ol] = (uint8_t)(int)p.z;
@@ -101,7 +204,7 @@ __global__ void __launch_bounds__(kGqWarps * 32) gptq_pack_w2_kernel(const void*
                 const uint32_t t[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
                 for (int i = 0; i < 16; ++i) word |= ((t[i >> 2] >> (8 * (i & 3))) & 3u) << (2 * i);
-                if ((lane & (lpg - 1)) == 0) s_zero[lane / lpg][ol] = zin[o * ng + k / group] & 3u;
+                if ((lane & (lpg - 1)) == 0) s_zero[lane >> (lg - 4)][ol] = zin[o * ng + (k >> lg)] & 3u;
             }
         }
         s_word[lane][ol] = word;
@@ -114,8 +217,8 @@ __global__ void __launch_bounds__(kGqWarps * 32) gptq_pack_w2_kernel(const void*
         if (r0 + r < nrow && o0 + lane < OC) qweight[(r0 + r) * OC + o0 + lane] = s_word[r][lane];
     }
     // scales [IC/G, OC] bf16 and qzeros [IC/G, OC/16]
-    const int gpt = kGqTileK / group;               // groups per tile
-    const int64_t g0 = k0 / group;
+    const int gpt = kGqTileK >> lg;                 // groups per tile
+    const int64_t g0 = k0 >> lg;
     for (int g = warp; g < gpt; g += kGqWarps) {
         if (g0 + g >= ng) break;
         const bool o_ok = o0 + lane < OC;

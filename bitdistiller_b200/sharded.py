@@ -359,6 +359,91 @@ class ShardGather:
         return gw
 
 
+class ShardGatherGroup:
+    """ShardGather for a GROUP of weights that are gathered together (FSDP2 gathers the parameters of one decoder layer in
+    one all-gather): one gather buffer for the group, laid out as the concatenation of the tensors' payloads -- which is
+    the payload of the concatenated (flat) weight, so ONE decode launch rebuilds every tensor of the group into one flat
+    buffer; the encode kernel runs once per tensor shard and stores into that tensor's slot of every rank's buffer.
+    `forward(list of w_shard)` -> list of fake-quantised full weights (views of the flat buffer, overwritten by the next
+    call)."""
+
+    def __init__(self, shapes, group_size, dtype, device, group=None, symmetric=True, round_mode=None):
+        from . import _lib as L
+        self.shapes, self.group_size, self.dtype, self.device, self.pg = list(shapes), group_size, dtype, torch.device(device), group
+        on = dist.is_available() and dist.is_initialized()
+        self.rank = dist.get_rank(group) if on else 0
+        self.world = dist.get_world_size(group) if on else 1
+        self.round_mode = L.ROUND_HALF_AWAY if round_mode is None else round_mode
+        self.layouts = [payload_layout(r, c, group_size, self.world) for r, c in self.shapes]
+        self.elems = [r * c for r, c in self.shapes]
+        self.code_base, self.sz_base, co, so = [], [], 0, 0
+        for (r, c) in self.shapes:
+            self.code_base.append(co)
+            self.sz_base.append(so)
+            co += r * c // 4
+            so += r * (c // group_size) * 4
+        self.ncode, self.nsz = co, so
+        self.symmetric = bool(symmetric) and self.world > 1
+        if self.symmetric:
+            import torch.distributed._symmetric_memory as symm_mem
+            self.buf = symm_mem.empty(co + so, dtype=torch.uint8, device=self.device)
+            self.hdl = symm_mem.rendezvous(self.buf, self.pg if self.pg is not None else dist.group.WORLD)
+            self.ptrs = [int(p) for p in self.hdl.buffer_ptrs]
+        else:
+            self.buf = torch.empty(co + so, dtype=torch.uint8, device=self.device)
+            self.ptrs = [self.buf.data_ptr()]
+        self.codes, self.sz = self.buf[:co], self.buf[co:]
+        self.flat = torch.empty(sum(self.elems), dtype=dtype, device=self.device)
+        self.views, off = [], 0
+        for (r, c), n in zip(self.shapes, self.elems):
+            self.views.append(self.flat[off:off + n].view(r, c))
+            off += n
+
+    def _encode_all(self, shards):
+        import ctypes
+
+        from . import _lib as L
+        base = self.buf.data_ptr()
+        peers = [p for i, p in enumerate(self.ptrs) if i != self.rank] if self.symmetric else []
+        st = L.stream_ptr(self.device)
+        with torch.cuda.device(self.device):
+            for t, w_shard in enumerate(shards):
+                r0, r1, coff, cbytes, soff, sbytes = self.layouts[t][self.rank]
+                assert w_shard.shape == (r1 - r0, self.shapes[t][1]) and w_shard.dtype == self.dtype
+                L.require_cuda(w_shard)
+                w = w_shard.detach().contiguous()
+                c0, s0 = self.code_base[t] + coff, self.ncode + self.sz_base[t] + soff
+                pc = (ctypes.c_void_p * max(len(peers), 1))(*[p + c0 for p in peers])
+                ps = (ctypes.c_void_p * max(len(peers), 1))(*[p + s0 for p in peers])
+                rc = L.lib().bdq_int2_shard_encode(L.ptr(w), ctypes.c_void_p(base + c0), ctypes.c_void_p(base + s0), L.i64(w.numel()),
+                                                   int(self.group_size), L.dtype_code(w), int(self.round_mode), L.semantics(),
+                                                   len(peers), pc, ps, st)
+                L.check(rc, "bdq_int2_shard_encode")
+
+    @torch.no_grad()
+    def forward(self, shards):
+        from . import _lib as L
+        if self.symmetric:
+            self.hdl.barrier(channel=0)
+            self._encode_all(shards)
+            self.hdl.barrier(channel=0)
+        else:
+            self._encode_all(shards)
+            if self.world > 1:                       # collective transport: per tensor, ragged slots padded
+                for t in range(len(self.shapes)):
+                    _, _, coff, cb, soff, sb = self.layouts[t][self.rank]
+                    c0, s0 = self.code_base[t], self.sz_base[t]
+                    codes, sz = gather_payload(self.codes[c0 + coff:c0 + coff + cb], self.sz[s0 + soff:s0 + soff + sb],
+                                               self.layouts[t], self.pg)
+                    self.codes[c0:c0 + codes.numel()] = codes
+                    self.sz[s0:s0 + sz.numel()] = sz
+        with torch.cuda.device(self.device):
+            rc = L.lib().bdq_int2_shard_decode(L.ptr(self.codes), L.ptr(self.sz), L.ptr(self.flat), L.i64(self.flat.numel()),
+                                               int(self.group_size), L.dtype_code(self.flat), L.stream_ptr(self.device))
+        L.check(rc, "bdq_int2_shard_decode")
+        return self.views
+
+
 class _ShardGatherFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, w_shard, gatherer, average):

@@ -125,6 +125,21 @@ def test_autograd_matches_ste_quantizer():
     assert torch.equal(a.grad.view(torch.int16), b.grad.view(torch.int16))
 
 
+def test_group_gather_one_decode_launch_equals_per_tensor():
+    from bitdistiller_b200 import _lib as L
+    from bitdistiller_b200 import sharded as S
+    from bitdistiller_b200.quantizer import SteInt2AsymQuantizer
+    shapes = [(64, 512), (64, 512), (176, 512), (64, 1408)]
+    ws = [(torch.randn(r, c, device=dev()) * 0.02).bfloat16() for r, c in shapes]
+    g = S.ShardGatherGroup(shapes, 128, torch.bfloat16, dev(), symmetric=False)
+    n0 = L.launch_count()
+    outs = g.forward(ws)
+    assert L.launch_count() - n0 == len(shapes) + 1          # one encode per tensor shard, ONE decode for the group
+    q = SteInt2AsymQuantizer(128)
+    for w, o in zip(ws, outs):
+        assert o.shape == w.shape and torch.equal(o.view(torch.int16), q(w).view(torch.int16))
+
+
 def test_errors():
     from bitdistiller_b200 import _lib as L
     lib = L.lib()

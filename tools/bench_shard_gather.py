@@ -117,17 +117,27 @@ def multi(dev, rank, world):
             if keep is not None:
                 keep.append(dq)
 
-    a, b, c = [], [], []
-    ref_order(0, a), nccl_payload(0, b), fused_path(0, c)
+    grp = S.ShardGatherGroup([(co, ci) for _, co, ci in LLAMA_LAYER], G, torch.bfloat16, dev, symmetric=True)
+
+    def fused_group(i, keep=None):
+        views = grp.forward(shards)                  # 7 encodes, one barrier pair, ONE decode over the layer's flat payload
+        if keep is not None:
+            keep.extend(v.clone() for v in views)
+
+    a, b, c, d = [], [], [], []
+    ref_order(0, a), nccl_payload(0, b), fused_path(0, c), fused_group(0, d)
+    same_grp = all(torch.equal(x.view(torch.int16), y.view(torch.int16)) for x, y in zip(a, d))
+    del d
     torch.cuda.synchronize(dev)
     same = all(torch.equal(x.view(torch.int16), y.view(torch.int16)) and torch.equal(x.view(torch.int16), z.view(torch.int16))
                for x, y, z in zip(a, b, c))
     local_ref = all(torch.equal(int_fakequant(w, 2, G, L.ROUND_HALF_AWAY)[0].view(torch.int16), x.view(torch.int16))
                     for w, x in zip(full, c))
     del a, b, c
-    out = {"world": world, "bit_equal_three_ways": bool(same), "bit_equal_to_unsharded": bool(local_ref),
+    out = {"world": world, "bit_equal_three_ways": bool(same), "bit_equal_group": bool(same_grp), "bit_equal_to_unsharded": bool(local_ref),
            "weights_per_layer": sum(w.numel() for w in full)}
-    for name, f in [("reference_order_bf16_allgather_then_quant", ref_order), ("nccl_payload", nccl_payload), ("fused_peer_stores", fused_path)]:
+    for name, f in [("reference_order_bf16_allgather_then_quant", ref_order), ("nccl_payload", nccl_payload), ("fused_peer_stores", fused_path),
+                    ("fused_peer_stores_layer_group_one_decode", fused_group)]:
         timed(f, 3, dev)
         out[name + "_ms_per_layer"] = timed(f, 20, dev)
     n = out["weights_per_layer"]
