@@ -29,6 +29,15 @@ struct GatherDst {
     int n;
 };
 
+// several shards in one launch (the tensors of one decoder layer): chunk (= 32 elements) index space is the concatenation
+struct GatherSegs {
+    const uint8_t* w[kMaxDst];
+    int64_t begin[kMaxDst];      // first chunk of the segment in the concatenated index space (multiple of G / 32)
+    int64_t code_off[kMaxDst];   // byte offset of the segment's codes / (scale, zero) pairs inside every destination
+    int64_t sz_off[kMaxDst];
+    int n;
+};
+
 template <int DT>
 struct Magic;
 template <>
@@ -55,9 +64,9 @@ __device__ __forceinline__ uint32_t lane_group_mask(int lane) {
     return ((LPG == 32) ? 0xffffffffu : ((1u << LPG) - 1u)) << (lane & ~(LPG - 1));
 }
 
-template <int DT, int G, int RM>
+template <int DT, int G, int RM, bool MULTI>
 __global__ void __launch_bounds__(kGatherThreads) int2_encode_kernel(const uint8_t* __restrict__ w, GatherDst dst, int64_t nchunk,
-                                                                     int sem) {
+                                                                     int sem, GatherSegs segs) {
     using P = P2<DT>;
     using h2 = typename P::h2;
     constexpr int LPG = G / 32;
@@ -68,8 +77,17 @@ __global__ void __launch_bounds__(kGatherThreads) int2_encode_kernel(const uint8
     const int64_t nwarps = (int64_t)gridDim.x * (kGatherThreads / 32);
     const int64_t nwc = (nchunk + 31) / 32;
     for (int64_t wc = warp; wc < nwc; wc += nwarps) {
-        const int64_t idx = wc * 32 + lane;
-        const bool valid = idx < nchunk;
+        const int64_t gidx = wc * 32 + lane;
+        const bool valid = gidx < nchunk;
+        int64_t idx = gidx, coff = 0, soff = 0;
+        if constexpr (MULTI) {
+            int sgi = 0;
+            for (int q = 1; q < segs.n; ++q) sgi = gidx >= segs.begin[q] ? q : sgi;
+            idx = gidx - segs.begin[sgi];
+            w = segs.w[sgi];
+            coff = segs.code_off[sgi];
+            soff = segs.sz_off[sgi];
+        }
         U8 raw[2];
         if (valid) {
             raw[0] = ldg256(w + idx * 64);
@@ -132,8 +150,8 @@ __global__ void __launch_bounds__(kGatherThreads) int2_encode_kernel(const uint8
             const int64_t g = idx / LPG;
 #pragma unroll 1
             for (int d = 0; d < dst.n; ++d) {
-                *reinterpret_cast<uint2*>(dst.codes[d] + idx * 8) = cw;
-                if (lig == 0) *reinterpret_cast<uint32_t*>(dst.sz[d] + g * 4) = P::bits(szp);
+                *reinterpret_cast<uint2*>(dst.codes[d] + coff + idx * 8) = cw;
+                if (lig == 0) *reinterpret_cast<uint32_t*>(dst.sz[d] + soff + g * 4) = P::bits(szp);
             }
         }
     }
@@ -180,14 +198,24 @@ static int check_shard(int64_t n_elem, int group, int dtype) {
 
 static int64_t gather_blocks(int64_t nchunk) { return ((nchunk + 31) / 32 + (kGatherThreads / 32) - 1) / (kGatherThreads / 32); }
 
-template <int DT, int RM>
-static void encode_g(const uint8_t* w, const GatherDst& dst, int64_t nchunk, int G, int sem, cudaStream_t st) {
+template <int DT, int RM, bool MULTI>
+static void encode_g2(const uint8_t* w, const GatherDst& dst, int64_t nchunk, int G, int sem, const GatherSegs& segs, cudaStream_t st) {
     const int64_t nb = gather_blocks(nchunk);
-#define BDQ_L(GG) int2_encode_kernel<DT, GG, RM><<<wave_grid(int2_encode_kernel<DT, GG, RM>, kGatherThreads, nb, 16), kGatherThreads, 0, st>>>(w, dst, nchunk, sem)
+#define BDQ_L(GG) int2_encode_kernel<DT, GG, RM, MULTI><<<wave_grid(int2_encode_kernel<DT, GG, RM, MULTI>, kGatherThreads, nb, 16), kGatherThreads, 0, st>>>(w, dst, nchunk, sem, segs)
     if (G == 128) BDQ_L(128);
     else if (G == 64) BDQ_L(64);
     else BDQ_L(32);
 #undef BDQ_L
+}
+
+template <int DT, int RM>
+static void encode_g(const uint8_t* w, const GatherDst& dst, int64_t nchunk, int G, int sem, const GatherSegs* segs, cudaStream_t st) {
+    if (segs) encode_g2<DT, RM, true>(w, dst, nchunk, G, sem, *segs, st);
+    else {
+        GatherSegs none;
+        none.n = 0;
+        encode_g2<DT, RM, false>(w, dst, nchunk, G, sem, none, st);
+    }
 }
 
 template <int DT>
@@ -204,14 +232,13 @@ static void decode_g(const uint8_t* codes, const uint8_t* sz, uint8_t* dq, int64
 
 using namespace bdq;
 
-extern "C" int bdq_int2_shard_encode(const void* w, void* codes, void* sz, int64_t n_elem, int group, int dtype, int round_mode,
-                                     int sem, int n_peer, void* const* peer_codes, void* const* peer_sz, bdq_stream_t stream) {
-    int rc = check_shard(n_elem, group, dtype);
-    if (rc) return rc;
-    if (round_mode != BDQ_ROUND_HALF_EVEN && round_mode != BDQ_ROUND_HALF_AWAY) { set_error("shard encode: bad round_mode %d", round_mode); return BDQ_ERR_UNSUPPORTED; }
-    if (n_peer < 0 || n_peer > kMaxDst - 1) { set_error("shard encode: n_peer=%d, at most %d", n_peer, kMaxDst - 1); return BDQ_ERR_SHAPE; }
+static int shard_encode_impl(const void* w, const GatherSegs* segs, void* codes, void* sz, int64_t n_elem, int group, int dtype,
+                             int round_mode, int sem, int n_peer, void* const* peer_codes, void* const* peer_sz, bdq_stream_t stream,
+                             const char* what) {
+    if (round_mode != BDQ_ROUND_HALF_EVEN && round_mode != BDQ_ROUND_HALF_AWAY) { set_error("%s: bad round_mode %d", what, round_mode); return BDQ_ERR_UNSUPPORTED; }
+    if (n_peer < 0 || n_peer > kMaxDst - 1) { set_error("%s: n_peer=%d, at most %d", what, n_peer, kMaxDst - 1); return BDQ_ERR_SHAPE; }
     if (n_elem == 0) return BDQ_OK;
-    if (!w || !codes || !sz || (n_peer > 0 && (!peer_codes || !peer_sz))) { set_error("null tensor pointer"); return BDQ_ERR_SHAPE; }
+    if (!codes || !sz || (n_peer > 0 && (!peer_codes || !peer_sz))) { set_error("null tensor pointer"); return BDQ_ERR_SHAPE; }
     GatherDst dst;
     dst.n = 1 + n_peer;
     dst.codes[0] = (uint8_t*)codes;
@@ -220,23 +247,60 @@ extern "C" int bdq_int2_shard_encode(const void* w, void* codes, void* sz, int64
         dst.codes[1 + i] = (uint8_t*)peer_codes[i];
         dst.sz[1 + i] = (uint8_t*)peer_sz[i];
     }
-    if ((uintptr_t)w % 32) { set_error("shard encode: w must be 32-byte aligned"); return BDQ_ERR_ALIGN; }
     for (int d = 0; d < dst.n; ++d)
         if (!dst.codes[d] || !dst.sz[d] || ((uintptr_t)dst.codes[d] % 8) || ((uintptr_t)dst.sz[d] % 4)) {
-            set_error("shard encode: destination %d null or misaligned (codes 8 B, scale/zero 4 B)", d);
+            set_error("%s: destination %d null or misaligned (codes 8 B, scale/zero 4 B)", what, d);
             return BDQ_ERR_ALIGN;
         }
     cudaStream_t st = (cudaStream_t)stream;
     const int64_t nchunk = n_elem / 32;
     const uint8_t* wp = (const uint8_t*)w;
     if (dtype == BDQ_BF16) {
-        if (round_mode == BDQ_ROUND_HALF_AWAY) encode_g<kBF16, BDQ_ROUND_HALF_AWAY>(wp, dst, nchunk, group, sem, st);
-        else encode_g<kBF16, BDQ_ROUND_HALF_EVEN>(wp, dst, nchunk, group, sem, st);
+        if (round_mode == BDQ_ROUND_HALF_AWAY) encode_g<kBF16, BDQ_ROUND_HALF_AWAY>(wp, dst, nchunk, group, sem, segs, st);
+        else encode_g<kBF16, BDQ_ROUND_HALF_EVEN>(wp, dst, nchunk, group, sem, segs, st);
     } else {
-        if (round_mode == BDQ_ROUND_HALF_AWAY) encode_g<kF16, BDQ_ROUND_HALF_AWAY>(wp, dst, nchunk, group, sem, st);
-        else encode_g<kF16, BDQ_ROUND_HALF_EVEN>(wp, dst, nchunk, group, sem, st);
+        if (round_mode == BDQ_ROUND_HALF_AWAY) encode_g<kF16, BDQ_ROUND_HALF_AWAY>(wp, dst, nchunk, group, sem, segs, st);
+        else encode_g<kF16, BDQ_ROUND_HALF_EVEN>(wp, dst, nchunk, group, sem, segs, st);
     }
-    return check_launch("bdq_int2_shard_encode");
+    return check_launch(what);
+}
+
+extern "C" int bdq_int2_shard_encode(const void* w, void* codes, void* sz, int64_t n_elem, int group, int dtype, int round_mode,
+                                     int sem, int n_peer, void* const* peer_codes, void* const* peer_sz, bdq_stream_t stream) {
+    int rc = check_shard(n_elem, group, dtype);
+    if (rc) return rc;
+    if (n_elem > 0 && !w) { set_error("null tensor pointer"); return BDQ_ERR_SHAPE; }
+    if ((uintptr_t)w % 32) { set_error("shard encode: w must be 32-byte aligned"); return BDQ_ERR_ALIGN; }
+    return shard_encode_impl(w, nullptr, codes, sz, n_elem, group, dtype, round_mode, sem, n_peer, peer_codes, peer_sz, stream,
+                             "bdq_int2_shard_encode");
+}
+
+extern "C" int bdq_int2_shard_encode_multi(int nseg, const void* const* w, const int64_t* n_elem, const int64_t* code_off,
+                                           const int64_t* sz_off, void* codes, void* sz, int group, int dtype, int round_mode, int sem,
+                                           int n_peer, void* const* peer_codes, void* const* peer_sz, bdq_stream_t stream) {
+    if (nseg < 1 || nseg > kMaxDst || !w || !n_elem || !code_off || !sz_off) { set_error("shard encode multi: nseg=%d (1..%d), non-null arrays", nseg, kMaxDst); return BDQ_ERR_SHAPE; }
+    GatherSegs segs;
+    segs.n = 0;
+    int64_t total = 0;
+    for (int i = 0; i < nseg; ++i) {
+        int rc = check_shard(n_elem[i], group, dtype);
+        if (rc) return rc;
+        if (n_elem[i] == 0) continue;
+        if (!w[i]) { set_error("null tensor pointer"); return BDQ_ERR_SHAPE; }
+        if (((uintptr_t)w[i] % 32) || (code_off[i] % 8) || (sz_off[i] % 4) || code_off[i] < 0 || sz_off[i] < 0) {
+            set_error("shard encode multi: segment %d misaligned (w 32 B, code offset 8 B, scale/zero offset 4 B)", i);
+            return BDQ_ERR_ALIGN;
+        }
+        segs.w[segs.n] = (const uint8_t*)w[i];
+        segs.begin[segs.n] = total / 32;
+        segs.code_off[segs.n] = code_off[i];
+        segs.sz_off[segs.n] = sz_off[i];
+        ++segs.n;
+        total += n_elem[i];
+    }
+    if (total == 0) return BDQ_OK;
+    return shard_encode_impl(nullptr, &segs, codes, sz, total, group, dtype, round_mode, sem, n_peer, peer_codes, peer_sz, stream,
+                             "bdq_int2_shard_encode_multi");
 }
 
 extern "C" int bdq_int2_shard_decode(const void* codes, const void* sz, void* dq, int64_t n_elem, int group, int dtype,

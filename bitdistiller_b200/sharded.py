@@ -365,7 +365,8 @@ class ShardGatherGroup:
     the payload of the concatenated (flat) weight, so ONE decode launch rebuilds every tensor of the group into one flat
     buffer; the encode kernel runs once per tensor shard and stores into that tensor's slot of every rank's buffer.
     `forward(list of w_shard)` -> list of fake-quantised full weights (views of the flat buffer, overwritten by the next
-    call)."""
+    call).  The symmetric gather buffer is double-buffered, so ONE barrier per call suffices: passing the barrier of call i
+    (all encodes of call i are done) implies every rank has finished the decode of call i-1, whose buffer call i+1 reuses."""
 
     def __init__(self, shapes, group_size, dtype, device, group=None, symmetric=True, round_mode=None):
         from . import _lib as L
@@ -386,45 +387,62 @@ class ShardGatherGroup:
         self.symmetric = bool(symmetric) and self.world > 1
         if self.symmetric:
             import torch.distributed._symmetric_memory as symm_mem
-            self.buf = symm_mem.empty(co + so, dtype=torch.uint8, device=self.device)
-            self.hdl = symm_mem.rendezvous(self.buf, self.pg if self.pg is not None else dist.group.WORLD)
-            self.ptrs = [int(p) for p in self.hdl.buffer_ptrs]
+            self.half = (co + so + 511) // 512 * 512
+            self.buf2 = symm_mem.empty(2 * self.half, dtype=torch.uint8, device=self.device)
+            self.hdl = symm_mem.rendezvous(self.buf2, self.pg if self.pg is not None else dist.group.WORLD)
+            self.ptrs2 = [int(p) for p in self.hdl.buffer_ptrs]
+            self.flip = 0
+            self._select(0)
         else:
             self.buf = torch.empty(co + so, dtype=torch.uint8, device=self.device)
             self.ptrs = [self.buf.data_ptr()]
-        self.codes, self.sz = self.buf[:co], self.buf[co:]
+            self.codes, self.sz = self.buf[:co], self.buf[co:]
         self.flat = torch.empty(sum(self.elems), dtype=dtype, device=self.device)
         self.views, off = [], 0
         for (r, c), n in zip(self.shapes, self.elems):
             self.views.append(self.flat[off:off + n].view(r, c))
             off += n
 
+    def _select(self, which):
+        off = which * self.half
+        self.buf = self.buf2[off:off + self.ncode + self.nsz]
+        self.ptrs = [p + off for p in self.ptrs2]
+        self.codes, self.sz = self.buf[:self.ncode], self.buf[self.ncode:]
+
     def _encode_all(self, shards):
+        """All shards of the group in ONE launch (bdq_int2_shard_encode_multi, up to 8 segments per launch)."""
         import ctypes
 
         from . import _lib as L
         base = self.buf.data_ptr()
         peers = [p for i, p in enumerate(self.ptrs) if i != self.rank] if self.symmetric else []
         st = L.stream_ptr(self.device)
+        ws, coffs, soffs = [], [], []
+        for t, w_shard in enumerate(shards):
+            r0, r1, coff, cbytes, soff, sbytes = self.layouts[t][self.rank]
+            assert w_shard.shape == (r1 - r0, self.shapes[t][1]) and w_shard.dtype == self.dtype
+            L.require_cuda(w_shard)
+            ws.append(w_shard.detach().contiguous())
+            coffs.append(self.code_base[t] + coff)
+            soffs.append(self.sz_base[t] + soff)
+        pc = (ctypes.c_void_p * max(len(peers), 1))(*peers)
+        ps = (ctypes.c_void_p * max(len(peers), 1))(*[p + self.ncode for p in peers])
         with torch.cuda.device(self.device):
-            for t, w_shard in enumerate(shards):
-                r0, r1, coff, cbytes, soff, sbytes = self.layouts[t][self.rank]
-                assert w_shard.shape == (r1 - r0, self.shapes[t][1]) and w_shard.dtype == self.dtype
-                L.require_cuda(w_shard)
-                w = w_shard.detach().contiguous()
-                c0, s0 = self.code_base[t] + coff, self.ncode + self.sz_base[t] + soff
-                pc = (ctypes.c_void_p * max(len(peers), 1))(*[p + c0 for p in peers])
-                ps = (ctypes.c_void_p * max(len(peers), 1))(*[p + s0 for p in peers])
-                rc = L.lib().bdq_int2_shard_encode(L.ptr(w), ctypes.c_void_p(base + c0), ctypes.c_void_p(base + s0), L.i64(w.numel()),
-                                                   int(self.group_size), L.dtype_code(w), int(self.round_mode), L.semantics(),
-                                                   len(peers), pc, ps, st)
-                L.check(rc, "bdq_int2_shard_encode")
+            for i in range(0, len(ws), 8):
+                n = len(ws[i:i + 8])
+                rc = L.lib().bdq_int2_shard_encode_multi(
+                    n, (ctypes.c_void_p * n)(*[w.data_ptr() for w in ws[i:i + 8]]), (ctypes.c_int64 * n)(*[w.numel() for w in ws[i:i + 8]]),
+                    (ctypes.c_int64 * n)(*coffs[i:i + 8]), (ctypes.c_int64 * n)(*soffs[i:i + 8]), ctypes.c_void_p(base),
+                    ctypes.c_void_p(base + self.ncode), int(self.group_size), L.dtype_code(ws[0]), int(self.round_mode), L.semantics(),
+                    len(peers), pc, ps, st)
+                L.check(rc, "bdq_int2_shard_encode_multi")
 
     @torch.no_grad()
     def forward(self, shards):
         from . import _lib as L
         if self.symmetric:
-            self.hdl.barrier(channel=0)
+            self._select(self.flip)
+            self.flip ^= 1
             self._encode_all(shards)
             self.hdl.barrier(channel=0)
         else:

@@ -228,6 +228,15 @@ int bdq_int2_shard_encode(const void* w, void* codes, void* sz, int64_t n_elem, 
                           int sem, int n_peer, void* const* peer_codes, void* const* peer_sz, bdq_stream_t stream);
 int bdq_int2_shard_decode(const void* codes, const void* sz, void* dq, int64_t n_elem, int group, int dtype,
                           bdq_stream_t stream);
+/*
+ * Up to 8 shards (the tensors of one FSDP2 parameter group, e.g. a decoder layer) in ONE encode launch: segment i =
+ * w[i] with n_elem[i] elements, its payload goes to byte offsets code_off[i] / sz_off[i] of `codes` / `sz` and of every
+ * peer destination.  With the group's payload laid out as the concatenation of the tensors' payloads, one
+ * bdq_int2_shard_decode over the whole buffer rebuilds all tensors (sharded.ShardGatherGroup).
+ */
+int bdq_int2_shard_encode_multi(int nseg, const void* const* w, const int64_t* n_elem, const int64_t* code_off,
+                                const int64_t* sz_off, void* codes, void* sz, int group, int dtype, int round_mode, int sem,
+                                int n_peer, void* const* peer_codes, void* const* peer_sz, bdq_stream_t stream);
 
 /*
  * Two-sided clip-ratio grid search = auto_2clip_layer (quantization/autoclip.py:13-83), all candidates of all

@@ -129,15 +129,23 @@ def test_group_gather_one_decode_launch_equals_per_tensor():
     from bitdistiller_b200 import _lib as L
     from bitdistiller_b200 import sharded as S
     from bitdistiller_b200.quantizer import SteInt2AsymQuantizer
-    shapes = [(64, 512), (64, 512), (176, 512), (64, 1408)]
+    shapes = [(64, 512), (64, 512), (176, 512), (64, 1408), (16, 128), (48, 256), (16, 4096)]
     ws = [(torch.randn(r, c, device=dev()) * 0.02).bfloat16() for r, c in shapes]
     g = S.ShardGatherGroup(shapes, 128, torch.bfloat16, dev(), symmetric=False)
     n0 = L.launch_count()
     outs = g.forward(ws)
-    assert L.launch_count() - n0 == len(shapes) + 1          # one encode per tensor shard, ONE decode for the group
+    assert L.launch_count() - n0 == 2                        # ONE encode over all shards, ONE decode for the group
     q = SteInt2AsymQuantizer(128)
     for w, o in zip(ws, outs):
         assert o.shape == w.shape and torch.equal(o.view(torch.int16), q(w).view(torch.int16))
+    many = [(32, 256)] * 11                                  # more than 8 tensors: two encode launches
+    g2 = S.ShardGatherGroup(many, 64, torch.float16, dev(), symmetric=False)
+    w2 = [(torch.randn(32, 256, device=dev()) * 0.02).half() for _ in many]
+    n0 = L.launch_count()
+    o2 = g2.forward(w2)
+    assert L.launch_count() - n0 == 3
+    q64 = SteInt2AsymQuantizer(64)
+    assert all(torch.equal(o.view(torch.int16), q64(w).view(torch.int16)) for w, o in zip(w2, o2))
 
 
 def test_errors():
