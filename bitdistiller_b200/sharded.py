@@ -462,6 +462,60 @@ class ShardGatherGroup:
         return self.views
 
 
+    @torch.no_grad()
+    def backward(self, shards, g_fulls, average=False):
+        """Per tensor: reduce-scatter of the gradient w.r.t. the quantised weight, then the fused STE backward on the shard
+        (see ShardGather.backward)."""
+        from . import _lib as L
+        out = []
+        for t, (w_shard, g_full) in enumerate(zip(shards, g_fulls)):
+            if g_full is None:
+                out.append(None)
+                continue
+            r0, r1 = self.layouts[t][self.rank][:2]
+            cols = self.shapes[t][1]
+            g_full = g_full.to(self.dtype).contiguous()
+            if self.world > 1:
+                sizes = [l[1] - l[0] for l in self.layouts[t]]
+                if len(set(sizes)) == 1:
+                    g = torch.empty((r1 - r0, cols), dtype=self.dtype, device=g_full.device)
+                    dist.reduce_scatter_tensor(g, g_full, op=dist.ReduceOp.SUM, group=self.pg)
+                else:
+                    dist.all_reduce(g_full, op=dist.ReduceOp.SUM, group=self.pg)
+                    g = g_full[r0:r1].contiguous()
+                if average:
+                    g /= self.world
+            else:
+                g = g_full
+            w = w_shard.detach().contiguous()
+            gw = torch.empty_like(w)
+            with torch.cuda.device(w.device):
+                rc = L.lib().bdq_int_ste_bwd(L.ptr(w), L.ptr(g), L.ptr(gw), L.i64(w.numel()), int(self.group_size), 2,
+                                             L.dtype_code(w), L.semantics(), L.stream_ptr(w.device))
+            L.check(rc, "bdq_int_ste_bwd")
+            out.append(gw)
+        return out
+
+
+class _ShardGatherGroupFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, gatherer, average, *shards):
+        ctx.gatherer, ctx.average = gatherer, average
+        ctx.save_for_backward(*shards)
+        # the views alias the gatherer's flat buffer, which the next forward overwrites: hand out copies that autograd may keep
+        return tuple(v.clone() for v in gatherer.forward(list(shards)))
+
+    @staticmethod
+    def backward(ctx, *g_fulls):
+        return (None, None) + tuple(ctx.gatherer.backward(list(ctx.saved_tensors), list(g_fulls), ctx.average))
+
+
+def quantized_all_gather_group(shards, gatherer, average=False):
+    """Autograd entry for a parameter group: list of shard parameters -> tuple of fake-quantised full weights
+    (ShardGatherGroup: one encode launch, one barrier, one decode launch per call)."""
+    return _ShardGatherGroupFn.apply(gatherer, average, *shards)
+
+
 class _ShardGatherFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, w_shard, gatherer, average):

@@ -148,6 +148,26 @@ def test_group_gather_one_decode_launch_equals_per_tensor():
     assert all(torch.equal(o.view(torch.int16), q64(w).view(torch.int16)) for w, o in zip(w2, o2))
 
 
+def test_group_autograd_matches_ste_quantizer():
+    from bitdistiller_b200 import sharded as S
+    from bitdistiller_b200.quantizer import SteInt2AsymQuantizer
+    shapes = [(64, 512), (32, 1024), (16, 128)]
+    ws = [(torch.randn(r, c, device=dev()) * 0.02).bfloat16() for r, c in shapes]
+    gys = [torch.randn(r, c, device=dev()).bfloat16() for r, c in shapes]
+    a = [w.clone().requires_grad_(True) for w in ws]
+    b = [w.clone().requires_grad_(True) for w in ws]
+    g = S.ShardGatherGroup(shapes, 128, torch.bfloat16, dev(), symmetric=False)
+    outs = S.quantized_all_gather_group(a, g)
+    torch.autograd.backward(list(outs), gys)
+    q = SteInt2AsymQuantizer(128)
+    for x, gy, o in zip(b, gys, outs):
+        y = q(x)
+        assert torch.equal(o.view(torch.int16), y.view(torch.int16))
+        y.backward(gy)
+    for x, y in zip(a, b):
+        assert torch.equal(x.grad.view(torch.int16), y.grad.view(torch.int16))
+
+
 def test_errors():
     from bitdistiller_b200 import _lib as L
     lib = L.lib()
