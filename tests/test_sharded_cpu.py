@@ -104,3 +104,22 @@ def test_payload_layout_is_a_partition():
         assert all(l[2] % 8 == 0 and l[4] % 4 == 0 for l in lay)           # kernel alignment of every slot
     with pytest.raises(ValueError):
         S.payload_layout(16, 100, 128, 2)
+
+
+def test_shard_gather_group_offsets_partition_the_buffer():
+    """Host-side layout of ShardGatherGroup (no kernel call): tensor payloads are laid back to back, every offset keeps the
+    kernels' alignment, and the flat output views tile the flat buffer in tensor order."""
+    shapes = [(4096, 4096)] * 4 + [(11008, 4096)] * 2 + [(4096, 11008)]
+    g = S.ShardGatherGroup(shapes, 128, torch.bfloat16, "cpu", symmetric=False)
+    n = sum(r * c for r, c in shapes)
+    assert g.ncode == n // 4 and g.nsz == n // 128 * 4 and g.buf.numel() == g.ncode + g.nsz
+    assert g.code_base[0] == 0 and g.sz_base[0] == 0
+    for t in range(1, len(shapes)):
+        r, c = shapes[t - 1]
+        assert g.code_base[t] - g.code_base[t - 1] == r * c // 4 and g.sz_base[t] - g.sz_base[t - 1] == r * c // 128 * 4
+        assert g.code_base[t] % 8 == 0 and g.sz_base[t] % 4 == 0
+    assert g.flat.numel() == n and [tuple(v.shape) for v in g.views] == shapes
+    off = 0
+    for v, (r, c) in zip(g.views, shapes):
+        assert v.data_ptr() == g.flat.data_ptr() + 2 * off
+        off += r * c
