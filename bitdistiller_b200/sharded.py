@@ -344,6 +344,7 @@ class ShardGather:
                 g = torch.empty((r1 - r0, self.cols), dtype=self.dtype, device=g_full.device)
                 dist.reduce_scatter_tensor(g, g_full, op=dist.ReduceOp.SUM, group=self.pg)
             else:
+                g_full = g_full.clone()          # never reduce into the caller's gradient tensor
                 dist.all_reduce(g_full, op=dist.ReduceOp.SUM, group=self.pg)
                 g = g_full[r0:r1].contiguous()
             if average:
@@ -481,6 +482,7 @@ class ShardGatherGroup:
                     g = torch.empty((r1 - r0, cols), dtype=self.dtype, device=g_full.device)
                     dist.reduce_scatter_tensor(g, g_full, op=dist.ReduceOp.SUM, group=self.pg)
                 else:
+                    g_full = g_full.clone()          # never reduce into the caller's gradient tensor
                     dist.all_reduce(g_full, op=dist.ReduceOp.SUM, group=self.pg)
                     g = g_full[r0:r1].contiguous()
                 if average:

@@ -22,6 +22,7 @@ def main():
     dev = torch.device("cuda", local)
     dist.init_process_group("nccl", device_id=dev)
     ok = True
+    fails = []
     for rows, cols, G in [(4096, 4096, 128), (11008, 4096, 128), (256, 1024, 64)]:
         gen = torch.Generator(device=dev).manual_seed(7)                       # same full weight on every rank
         w_full = (torch.randn(rows, cols, device=dev, generator=gen) * 0.02).bfloat16()
@@ -45,11 +46,45 @@ def main():
         same_fwd = torch.equal(qw.view(torch.int16), q.detach().view(torch.int16))
         same_bwd = torch.equal(w_shard.grad.view(torch.int16), wf2.grad[r0:r1].contiguous().view(torch.int16))
         close = float((w_shard.grad.float() - wf2.grad[r0:r1].float()).abs().max()) <= 1e-2 * float(wf2.grad.float().abs().max())
-        ok = ok and same_fwd and (same_bwd or (world > 2 and close))           # > 2 ranks: the bf16 sum order may differ
+        if not (same_fwd and (same_bwd or (world > 2 and close))):
+            ok = False
+            fails.append(f'single {rows}x{cols} fwd={same_fwd} bwd={same_bwd} rank={rank}')           # > 2 ranks: the bf16 sum order may differ
+    # parameter group (one encode launch, one decode launch), both transports, forward and backward through autograd
+    shapes = [(4096, 4096), (11008, 4096), (4096, 11008), (272, 1024)]           # 272 rows: ragged shards for world > 1
+    gen = torch.Generator(device=dev).manual_seed(11)
+    fulls = [(torch.randn(r, c, device=dev, generator=gen) * 0.02).bfloat16() for r, c in shapes]
+    gys = [torch.randn(r, c, device=dev, generator=torch.Generator(device=dev).manual_seed(50 + rank)).bfloat16() for r, c in shapes]
+    refs, ref_grads = [], []
+    for wfull, gy in zip(fulls, gys):
+        gsum = gy.clone()
+        dist.all_reduce(gsum)
+        wr = wfull.clone().requires_grad_(True)
+        qr = SteInt2AsymQuantizer(128)(wr)
+        qr.backward(gsum)
+        refs.append(qr.detach())
+        ref_grads.append(wr.grad)
+    for symmetric in (True, False):
+        grp = S.ShardGatherGroup(shapes, 128, torch.bfloat16, dev, symmetric=symmetric)
+        spans = [S.row_shard(r, rank, world) for r, _ in shapes]
+        shards = [w[a:b].clone().requires_grad_(True) for w, (a, b) in zip(fulls, spans)]
+        outs = S.quantized_all_gather_group(shards, grp)
+        for ti, (o, r) in enumerate(zip(outs, refs)):
+            if not torch.equal(o.view(torch.int16), r.view(torch.int16)):
+                ok = False
+                fails.append(f'fwd sym={symmetric} t={ti} rank={rank}')
+        torch.autograd.backward(list(outs), gys)
+        for sh, rg, (a, b) in zip(shards, ref_grads, spans):
+            same = torch.equal(sh.grad.view(torch.int16), rg[a:b].contiguous().view(torch.int16))
+            close = float((sh.grad.float() - rg[a:b].float()).abs().max()) <= 1e-2 * float(rg.float().abs().max())
+            if not (same or (world > 2 and close)):
+                ok = False
+                fails.append(f'bwd sym={symmetric} shape={tuple(sh.shape)} rank={rank} maxdiff={float((sh.grad.float() - rg[a:b].float()).abs().max())}')
+    if fails:
+        print(rank, fails, flush=True)
     t = torch.tensor([int(ok)], device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MIN)
     if rank == 0:
-        print(json.dumps({"world": world, "shard_gradient_equals_full_weight_ste_backward_rows": bool(t.item())}), flush=True)
+        print(json.dumps({"world": world, "shard_gradient_equals_full_weight_ste_backward_rows": bool(t.item()), "includes": "ShardGather + ShardGatherGroup (symmetric and collective transport, ragged shards)"}), flush=True)
     dist.destroy_process_group()
 
 
