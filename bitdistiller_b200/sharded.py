@@ -258,6 +258,27 @@ def gather_payload(local_codes, local_sz, layout, group=None):
             torch.cat([recv[r, cmax: cmax + l[5]] for r, l in enumerate(layout)]))
 
 
+def reduce_scatter_rows(g_full, layout, rank, group=None, average=False):
+    """Sum over ranks of a [rows, cols] gradient, rows [r0, r1) of `layout[rank]` returned (the gradient half of the
+    quantise-before-all-gather path).  Even shards: one reduce-scatter; ragged shards: all-reduce of a COPY (the caller's
+    tensor is never written) and a slice.  Works on gloo/CPU tensors too."""
+    world = len(layout)
+    r0, r1 = layout[rank][:2]
+    if world == 1 or not (dist.is_available() and dist.is_initialized()):
+        return g_full
+    sizes = [l[1] - l[0] for l in layout]
+    if len(set(sizes)) == 1 and dist.get_backend(group) != "gloo":
+        g = torch.empty((r1 - r0, g_full.shape[1]), dtype=g_full.dtype, device=g_full.device)
+        dist.reduce_scatter_tensor(g, g_full.contiguous(), op=dist.ReduceOp.SUM, group=group)
+    else:
+        tmp = g_full.clone()
+        dist.all_reduce(tmp, op=dist.ReduceOp.SUM, group=group)
+        g = tmp[r0:r1].contiguous()
+    if average:
+        g /= world
+    return g
+
+
 class ShardGather:
     """Quantise-before-all-gather of ONE int2 QLinear weight [rows, cols] held as dim-0 shards (FSDP2 layout):
     `forward(w_shard)` returns the fake-quantised FULL weight on every rank, bit-equal to
@@ -336,21 +357,7 @@ class ShardGather:
     @torch.no_grad()
     def backward(self, w_shard, g_full, average=False):
         from . import _lib as L
-        r0, r1 = self.layout[self.rank][:2]
-        g_full = g_full.to(self.dtype).contiguous()
-        if self.world > 1:
-            sizes = [l[1] - l[0] for l in self.layout]
-            if len(set(sizes)) == 1:
-                g = torch.empty((r1 - r0, self.cols), dtype=self.dtype, device=g_full.device)
-                dist.reduce_scatter_tensor(g, g_full, op=dist.ReduceOp.SUM, group=self.pg)
-            else:
-                g_full = g_full.clone()          # never reduce into the caller's gradient tensor
-                dist.all_reduce(g_full, op=dist.ReduceOp.SUM, group=self.pg)
-                g = g_full[r0:r1].contiguous()
-            if average:
-                g /= self.world
-        else:
-            g = g_full
+        g = reduce_scatter_rows(g_full.to(self.dtype).contiguous(), self.layout, self.rank, self.pg, average)
         w = w_shard.detach().contiguous()
         gw = torch.empty_like(w)
         with torch.cuda.device(w.device):
@@ -473,22 +480,7 @@ class ShardGatherGroup:
             if g_full is None:
                 out.append(None)
                 continue
-            r0, r1 = self.layouts[t][self.rank][:2]
-            cols = self.shapes[t][1]
-            g_full = g_full.to(self.dtype).contiguous()
-            if self.world > 1:
-                sizes = [l[1] - l[0] for l in self.layouts[t]]
-                if len(set(sizes)) == 1:
-                    g = torch.empty((r1 - r0, cols), dtype=self.dtype, device=g_full.device)
-                    dist.reduce_scatter_tensor(g, g_full, op=dist.ReduceOp.SUM, group=self.pg)
-                else:
-                    g_full = g_full.clone()          # never reduce into the caller's gradient tensor
-                    dist.all_reduce(g_full, op=dist.ReduceOp.SUM, group=self.pg)
-                    g = g_full[r0:r1].contiguous()
-                if average:
-                    g /= self.world
-            else:
-                g = g_full
+            g = reduce_scatter_rows(g_full.to(self.dtype).contiguous(), self.layouts[t], self.rank, self.pg, average)
             w = w_shard.detach().contiguous()
             gw = torch.empty_like(w)
             with torch.cuda.device(w.device):

@@ -75,6 +75,15 @@ def _worker(rank, world, port, q):
         _, _, coff, cb, soff, sb = lay[rank]
         gc_, gs_ = S.gather_payload(allc[coff:coff + cb], alls[soff:soff + sb], lay)
         ok = ok and torch.equal(gc_, allc) and torch.equal(gs_, alls)
+        # gradient half of the quantise-before-all-gather path: sum over ranks, own rows back, caller's tensor untouched
+        for rows in (48, 64):                                  # 48 rows -> ragged shards (16 / 32), 64 -> even
+            lay2 = S.payload_layout(rows, 128, 128, world)
+            mine = torch.full((rows, 128), float(rank + 1)) + torch.arange(rows, dtype=torch.float32).view(-1, 1)
+            keep = mine.clone()
+            got = S.reduce_scatter_rows(mine, lay2, rank)
+            r0, r1 = lay2[rank][:2]
+            want = (3.0 + 2 * torch.arange(rows, dtype=torch.float32).view(-1, 1)).expand(rows, 128)[r0:r1]
+            ok = ok and torch.equal(got, want) and torch.equal(mine, keep)
         q.put((rank, bool(ok)))
     finally:
         dist.destroy_process_group()
