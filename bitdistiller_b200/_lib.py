@@ -26,9 +26,17 @@ class BdqError(RuntimeError):
 
 
 def semantics():
-    """Eager-device rounding semantics to reproduce: BDQ_SEMANTICS=cpu (default, the
-    golden-vector-pinned behaviour of the reference on CPU) or cuda (reciprocal-multiply / fp32 compares)."""
-    return SEM_CUDA if os.environ.get("BDQ_SEMANTICS", "cpu").lower() == "cuda" else SEM_CPU
+    """Eager-device rounding semantics to reproduce: `tensor / python_scalar` is a true division in
+    CPU eager and a multiply by the fp32 reciprocal in CUDA eager, so the reference's scales differ by 1 ulp in ~1/3 of
+    the groups between the two devices.  Default = `cuda`: this package runs on CUDA tensors only, and every real flow of
+    the reference (QAT, run_clip, real_quantize_model_weight) quantises on the GPU, so a user swapping the import gets the
+    bits the reference produces on that same GPU (pinned on the B200 against the unmodified reference in CUDA eager,
+    tests/test_reference_gpu.py).  BDQ_SEMANTICS=cpu reproduces the reference's CPU results (pinned by tests/golden/*.npz,
+    which can only be generated on the GPU-less build container); tests/conftest.py selects it for the golden tests."""
+    v = os.environ.get("BDQ_SEMANTICS", "cuda").lower()
+    if v not in ("cuda", "cpu"):
+        raise BdqError(f"BDQ_SEMANTICS must be 'cuda' or 'cpu', got {v!r}")
+    return SEM_CUDA if v == "cuda" else SEM_CPU
 
 
 def lib():

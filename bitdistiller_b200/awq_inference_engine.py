@@ -105,3 +105,69 @@ def gemm_forward_cuda(in_feats, kernel, scaling_factors, zeros, group_size, spli
     if w_bit != 2:
         raise NotImplementedError("only the 2-bit packed GEMM is implemented")
     return gemm_w2(in_feats, kernel, scaling_factors, zeros, group_size)
+
+
+class _Phase(__import__("ctypes").Structure):
+    """bdq_gemv_phase_t (include/bdq.h)."""
+    import ctypes as _c
+    _fields_ = [("x", _c.c_void_p), ("nmat", _c.c_int), ("group", _c.c_int), ("flags", _c.c_int), ("reserved", _c.c_int),
+                ("IC", _c.c_int64), ("qweight", _c.c_void_p * 4), ("scales", _c.c_void_p * 4), ("qzeros", _c.c_void_p * 4),
+                ("out", _c.c_void_p * 4), ("OC", _c.c_int64 * 4)]
+
+
+GEMV_CHAIN_NOWAIT = 256
+
+
+class DecodeChain:
+    """A decoded token's batch-1 GEMVs as ONE persistent launch (bdq_gemv_w2_chain_*): the per-linear
+    `gemv_forward_cuda` calls of WQLinear.forward (quantization/qmodule.py:166) for a whole token, grouped into phases of
+    up to 4 matrices that share their activation vector (fused q/k/v, gate/up: inference/modules/fused_attn.py:304-340,
+    fused_mlp.py:44-114).  `phases`: list of dicts
+        {"x": [1, IC] fp16 tensor, "mats": [(qweight, scales, qzeros, out [1, OC] fp16), ...], "silu": False, "nowait": False}
+    executed in order; phase p reads x after every earlier phase has stored its outputs, so x may be an `out` of an
+    earlier phase ("nowait": x is an external input, no dependency).  run() is bit-equal to issuing the phases as
+    gemv_multi_forward_cuda / gemv_silu_mul_forward_cuda launches one after the other.  The tensors are referenced by
+    address: keep them alive and do not reallocate them."""
+
+    def __init__(self, phases, group_size=128):
+        import ctypes
+        if not phases:
+            raise ValueError("DecodeChain needs at least one phase")
+        self._keep = []
+        arr = (_Phase * len(phases))()
+        dev = phases[0]["x"].device
+        self.max_ic = 0
+        for p, ph in enumerate(phases):
+            x, mats = ph["x"], ph["mats"]
+            L.require_cuda(x, *[t for m in mats for t in m if t is not None])
+            _check_fp16(x, *[m[1] for m in mats])
+            if x.numel() != x.shape[-1] or not x.is_contiguous():
+                raise ValueError("DecodeChain is the batch-1 decode path: every x must hold one contiguous row")
+            if not 1 <= len(mats) <= 4:
+                raise ValueError("a phase takes 1..4 matrices")
+            a = arr[p]
+            a.x, a.nmat, a.group, a.IC = x.data_ptr(), len(mats), int(group_size), x.shape[-1]
+            a.flags = (GEMV_SILU_MUL if ph.get("silu") else 0) | (GEMV_CHAIN_NOWAIT if ph.get("nowait") else 0)
+            for i, (qw, sc, qz, out) in enumerate(mats):
+                assert qw.is_contiguous() and sc.is_contiguous() and qz.is_contiguous() and qw.shape[1] * 16 == x.shape[-1]
+                a.qweight[i], a.scales[i], a.qzeros[i] = qw.data_ptr(), sc.data_ptr(), qz.data_ptr()
+                a.out[i] = 0 if out is None else out.data_ptr()
+                a.OC[i] = qw.shape[0]
+                self._keep += [qw, sc, qz, out]
+            self._keep.append(x)
+            self.max_ic = max(self.max_ic, x.shape[-1])
+        self.n, self.device = len(phases), dev
+        lib = L.lib()
+        lib.bdq_gemv_w2_chain_workspace_bytes.restype = ctypes.c_int64
+        nbytes = int(lib.bdq_gemv_w2_chain_workspace_bytes(self.n))
+        self.workspace = torch.zeros(nbytes + 256, dtype=torch.uint8, device=dev)
+        off = (-self.workspace.data_ptr()) % 256
+        self._ws = ctypes.c_void_p(self.workspace.data_ptr() + off)
+        with torch.cuda.device(dev):
+            rc = lib.bdq_gemv_w2_chain_prepare(arr, self.n, self._ws, L.i64(nbytes), L.stream_ptr(dev))
+        L.check(rc, "bdq_gemv_w2_chain_prepare")
+
+    def run(self, lookahead=2):
+        with torch.cuda.device(self.device):
+            rc = L.lib().bdq_gemv_w2_chain_run(self._ws, self.n, L.i64(self.max_ic), int(lookahead), L.stream_ptr(self.device))
+        L.check(rc, "bdq_gemv_w2_chain_run")

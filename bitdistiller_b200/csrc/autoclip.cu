@@ -369,12 +369,7 @@ template <int DT>
 static int launch_autoclip(const AcArgs& a, cudaStream_t st) {
     using C = AcCfg<DT>;
     const AcSmem L = ac_layout(a.G, C::KMUL, C::TCH);
-    static bool attr_done = false;
-    if (!attr_done) {
-        if (cudaFuncSetAttribute(autoclip_kernel<DT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess)
-            return check_launch("bdq_autoclip(attr)");
-        attr_done = true;
-    }
+    if (!ensure_dyn_smem(reinterpret_cast<const void*>(autoclip_kernel<DT>), 227 * 1024)) return check_launch("bdq_autoclip(attr)");
     dim3 grid((unsigned)(a.ci / a.G), (unsigned)((a.co + kAcOT - 1) / kAcOT));
     autoclip_kernel<DT><<<grid, C::THREADS, (size_t)L.total, st>>>(a);
     return check_launch("bdq_autoclip");

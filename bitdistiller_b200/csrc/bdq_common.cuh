@@ -15,6 +15,7 @@ constexpr int kF32 = BDQ_F32, kBF16 = BDQ_BF16, kF16 = BDQ_F16;
 void set_error(const char* fmt, ...);
 int check_launch(const char* what);
 int sm_count();
+bool ensure_dyn_smem(const void* fn, int bytes);   // per (device, kernel): see runtime.cu
 
 // Grid of a persistent, warp-strided streaming kernel: a whole number of waves (resident CTAs per SM x SMs x waves), so
 // that no partial last wave leaves SMs idle.  Several short waves balance better than one long one (the SMs do not all

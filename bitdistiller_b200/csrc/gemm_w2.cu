@@ -323,13 +323,9 @@ int launch_gemm_w2(const void* x, const int32_t* qweight, const void* scales, co
                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) { set_error("gemm_w2: cuTensorMapEncodeTiled failed (%d)", (int)r); return BDQ_ERR_CUDA; }
-    static bool attr_done = false;
-    if (!attr_done) {
-        if (cudaFuncSetAttribute(gemm_w2_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, GmCfg<1>::kSmem) != cudaSuccess ||
-            cudaFuncSetAttribute(gemm_w2_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, GmCfg<2>::kSmem) != cudaSuccess)
-            return check_launch("bdq_gemm_w2(attr)");
-        attr_done = true;
-    }
+    if (!ensure_dyn_smem(reinterpret_cast<const void*>(gemm_w2_kernel<1>), GmCfg<1>::kSmem) ||
+        !ensure_dyn_smem(reinterpret_cast<const void*>(gemm_w2_kernel<2>), GmCfg<2>::kSmem))
+        return check_launch("bdq_gemm_w2(attr)");
     dim3 grid((unsigned)((OC + kGmN - 1) / kGmN), (unsigned)((M + kGmM * MT - 1) / (kGmM * MT)));
     if (MT == 2)
         gemm_w2_kernel<2><<<grid, kGmThreads, GmCfg<2>::kSmem, st>>>(map, (const uint32_t*)qweight, (const __half*)scales,

@@ -367,14 +367,9 @@ extern "C" int bdq_gemv_w2(const void* x, const int32_t* qweight, const void* sc
                                                      (const uint32_t*)qzeros, (__half*)out, (int)IC, (int)OC, group, zw);
         return check_launch("bdq_gemv_w2(generic)");
     }
-    static bool attr_done[2] = {false, false};
     const bool pdl = (flags & BDQ_GEMV_PDL) != 0;
     auto kern = pdl ? gemv_w2_g128_kernel<true> : gemv_w2_g128_kernel<false>;
-    if (!attr_done[pdl]) {
-        if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess)
-            return check_launch("bdq_gemv_w2(attr)");
-        attr_done[pdl] = true;
-    }
+    if (!ensure_dyn_smem(reinterpret_cast<const void*>(kern), 227 * 1024)) return check_launch("bdq_gemv_w2(attr)");
     const int nsm = sm_count();
     for (int64_t b0 = 0; b0 < B;) {
         // activation rows per launch: as many (<= 8) as leave room for at least 2 ring stages

@@ -660,14 +660,9 @@ int bdq_gemv_w2_stream_launch(const void* x, int nmat, const int32_t* const* qwe
                                     gemv_w2s_kernel<false, true, false>,  gemv_w2s_kernel<true, true, false>,
                                     gemv_w2s_kernel<false, false, true>,  gemv_w2s_kernel<true, false, true>,
                                     gemv_w2s_kernel<false, true, true>,   gemv_w2s_kernel<true, true, true>};
-    static bool attr_done[8] = {false, false, false, false, false, false, false, false};
     const int ai = (tma ? 4 : 0) + (prof ? 2 : 0) + (pdl ? 1 : 0);
     KernFn kern = kerns[ai];
-    if (!attr_done[ai]) {
-        if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024) != cudaSuccess)
-            return check_launch("bdq_gemv_w2(stream attr)");
-        attr_done[ai] = true;
-    }
+    if (!ensure_dyn_smem(reinterpret_cast<const void*>(kern), 112 * 1024)) return check_launch("bdq_gemv_w2(stream attr)");
     // two CTAs (16 warps) per SM; BDQ_GEMV_CTAS1 = one (leaves room for a PDL successor's CTA to prefetch)
     int grid = sm_count() * ((flags & BDQ_GEMV_CTAS1) ? 1 : 2);
     const int units = silu ? total_rb / 2 : total_rb;   // gate/up mode: CTAs own whole (gate, up) block pairs

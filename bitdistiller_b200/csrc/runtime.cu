@@ -39,6 +39,28 @@ int sm_count() {
     return cached[dev];
 }
 
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is per DEVICE: remember (device, function) pairs, so that a process
+// that drives several GPUs (HF device_map inference over WQLinear, autoclip on cuda:1 after cuda:0) sets it on each.
+bool ensure_dyn_smem(const void* fn, int bytes) {
+    struct Key { int dev; const void* fn; };
+    static Key done[512];
+    static int ndone = 0;
+    static std::atomic_flag lock = ATOMIC_FLAG_INIT;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return false;
+    while (lock.test_and_set(std::memory_order_acquire)) {}
+    bool found = false;
+    for (int i = 0; i < ndone; ++i)
+        if (done[i].dev == dev && done[i].fn == fn) { found = true; break; }
+    bool ok = true;
+    if (!found) {
+        ok = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) == cudaSuccess;
+        if (ok && ndone < 512) done[ndone++] = Key{dev, fn};
+    }
+    lock.clear(std::memory_order_release);
+    return ok;
+}
+
 }  // namespace bdq
 
 extern "C" int bdq_version(void) { return 100; }

@@ -446,7 +446,8 @@ class ShardGatherGroup:
                 L.check(rc, "bdq_int2_shard_encode_multi")
 
     @torch.no_grad()
-    def forward(self, shards):
+    def forward(self, shards, record=None):
+        """`record`: optional list; a (start, stop) CUDA-event pair around the decode launch is appended (bench.py)."""
         from . import _lib as L
         if self.symmetric:
             self._select(self.flip)
@@ -464,8 +465,14 @@ class ShardGatherGroup:
                     self.codes[c0:c0 + codes.numel()] = codes
                     self.sz[s0:s0 + sz.numel()] = sz
         with torch.cuda.device(self.device):
+            if record is not None:
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
             rc = L.lib().bdq_int2_shard_decode(L.ptr(self.codes), L.ptr(self.sz), L.ptr(self.flat), L.i64(self.flat.numel()),
                                                int(self.group_size), L.dtype_code(self.flat), L.stream_ptr(self.device))
+            if record is not None:
+                e1.record()
+                record.append((e0, e1))
         L.check(rc, "bdq_int2_shard_decode")
         return self.views
 

@@ -144,6 +144,41 @@ int bdq_gemv_w2_multi(const void* x, int nmat, const int32_t* const* qweight, co
                       int n_prefetch, const void* const* prefetch, const int64_t* prefetch_bytes, bdq_stream_t stream);
 
 /*
+ * Whole-token decode chain in ONE persistent launch.  A chain is an ordered list of phases; a phase is what one
+ * bdq_gemv_w2_multi call computes (up to 4 packed matrices sharing one activation vector x [IC] fp16, group 128,
+ * OC[i] % 16 == 0; BDQ_GEMV_SILU_MUL in `flags` as above).  Running the chain is equivalent -- bit for bit -- to issuing
+ * the phases as consecutive bdq_gemv_w2_multi launches on one stream: phase p reads x after every earlier phase has
+ * stored its outputs (so x may be the out[] of an earlier phase), unless the phase carries BDQ_GEMV_CHAIN_NOWAIT (its x
+ * is an external input that is ready at launch).  This replaces the per-linear gemv_forward_cuda launches of a decoded
+ * token (quantization/qmodule.py:166; inference/modules/fused_mlp.py:44-114, fused_attn.py:304-340 ->
+ * inference/kernels/csrc/quantization/gemv_cuda.cu:289-346): 2 CTAs per SM stay resident, a grid barrier on an L2 counter
+ * replaces the launch boundary between dependent phases, and one lane per CTA prefetches the packed weights of the next
+ * `lookahead` phases HBM -> L2 so that HBM keeps streaming while the CTAs wait.
+ *   bdq_gemv_w2_chain_workspace_bytes(n)  device bytes the caller must provide (256-byte aligned)
+ *   bdq_gemv_w2_chain_prepare(...)        validates the phases and writes the device-side plan (synchronous, once per model)
+ *   bdq_gemv_w2_chain_run(...)            one cooperative launch; max_IC = the largest IC of the plan; lookahead <= 0 -> 2
+ * The workspace also holds the barrier counters: two runs of the same workspace must not overlap (one stream).
+ */
+#define BDQ_GEMV_CHAIN_NOWAIT 256
+typedef struct bdq_gemv_phase {
+    const void* x;
+    int nmat;
+    int group;
+    int flags;
+    int reserved;
+    int64_t IC;
+    const int32_t* qweight[4];
+    const void* scales[4];
+    const int32_t* qzeros[4];
+    void* out[4];
+    int64_t OC[4];
+} bdq_gemv_phase_t;
+int64_t bdq_gemv_w2_chain_workspace_bytes(int n_phases);
+int bdq_gemv_w2_chain_prepare(const bdq_gemv_phase_t* phases, int n_phases, void* workspace, int64_t workspace_bytes,
+                              bdq_stream_t stream);
+int bdq_gemv_w2_chain_run(const void* workspace, int n_phases, int64_t max_IC, int lookahead, bdq_stream_t stream);
+
+/*
  * Packed NF3 (3 bits per weight + two fp16 scales per group).  The reference has no packed NF3 format or kernel
  * (quantization/qmodule.py:77 accepts w_bit 2 and 4 only), so the layout is this library's own; its contract is that
  * bdq_nf3_dequant(pack(w)) equals SteN2F3Quantizer.forward(w) / pseudo_quantize_n2f3_tensor(w)

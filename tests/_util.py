@@ -86,3 +86,25 @@ def make_weight(kind, rows, cols, dtype, seed):
     else:
         raise ValueError(kind)
     return w.to(dtype)
+
+
+def tiny_llama(seed=0, dtype=torch.bfloat16):
+    """Random-init Llama (2 layers, hidden 256) whose every parameter is drawn from a seeded CPU generator in
+    sorted-name order, so the GPU box rebuilds the identical model without shipping a state dict."""
+    from transformers import LlamaConfig, LlamaForCausalLM
+    cfg = LlamaConfig(hidden_size=256, intermediate_size=512, num_hidden_layers=2, num_attention_heads=4,
+                      num_key_value_heads=2, vocab_size=128, max_position_embeddings=64, tie_word_embeddings=False,
+                      attn_implementation="eager")
+    model = LlamaForCausalLM(cfg)
+    g = torch.Generator().manual_seed(seed)
+    with torch.no_grad():
+        for name, p in sorted(model.named_parameters()):
+            if p.dim() == 1:
+                p.copy_(1.0 + 0.1 * torch.randn(p.shape, generator=g))
+            else:
+                p.copy_(torch.randn(p.shape, generator=g) * (0.05 if "embed" in name or "lm_head" in name else 0.03))
+    return model.to(dtype)
+
+
+QL_GRADS = ["model.layers.0.self_attn.q_proj.weight", "model.layers.1.self_attn.k_proj.weight",
+            "model.layers.0.mlp.gate_proj.weight", "model.layers.1.mlp.down_proj.weight"]

@@ -16,7 +16,9 @@ OUT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, REF)
 sys.modules.setdefault("awq_inference_engine", types.ModuleType("awq_inference_engine"))
 
+sys.path.insert(0, os.path.dirname(OUT))
 import quantizer as rq  # noqa: E402
+from _util import QL_GRADS, tiny_llama  # noqa: E402
 
 DT = {"f32": torch.float32, "bf16": torch.bfloat16, "f16": torch.float16}
 
@@ -97,6 +99,7 @@ def gen_ste():
                     out[k + "_w"], out[k + "_gy"] = f32(w), f32(gy)
                     out[k + "_y"], out[k + "_gw"] = f32(res["T"][0]), f32(res["T"][1])
                     out[k + "_gw64"] = res["f64"][1].numpy()
+                    out[k + "_y64"] = res["f64"][0].numpy()  # where y64 == y the T run and the f64 run took the same codes
                     idx += 1
     # NaN behaviour of nf3 (min exactly 0 in a group)
     w = make_inputs("randn", 2, 256, torch.bfloat16, 77)
@@ -202,9 +205,32 @@ def gen_gptq():
     print("gptq", idx)
 
 
+def gen_qlinear():
+    """quantization/qlinear.py:5-78 -- the function train/train.py:448 calls: convertModelToQuant on a tiny Llama, one
+    forward + loss.backward() on CPU (bf16 compute), logits and four weight gradients stored."""
+    import qlinear as rl
+    out = {}
+    ids = torch.randint(0, 128, (2, 32), generator=torch.Generator().manual_seed(11))
+    out["ids"] = ids.numpy()
+    for qt in ["int2-asym", "ste-n2f3"]:
+        model = tiny_llama()
+        model, replaced = rl.convertModelToQuant(model, compute_dtype=torch.bfloat16, quant_type=qt, q_group_size=128)
+        assert replaced and isinstance(model.model.layers[0].mlp.up_proj, rl.QLinear)
+        assert not isinstance(model.lm_head, rl.QLinear)
+        res = model(input_ids=ids, labels=ids)
+        res.loss.backward()
+        out[qt + "_logits"] = f32(res.logits)
+        out[qt + "_loss"] = np.float64(res.loss.item())
+        params = dict(model.named_parameters())
+        for n in QL_GRADS:
+            out[qt + "_g_" + n] = f32(params[n].grad)
+    np.savez_compressed(os.path.join(OUT, "qlinear.npz"), **out)
+    print("qlinear", {k: v.shape for k, v in out.items() if k.endswith("logits")})
+
+
 if __name__ == "__main__":
     torch.manual_seed(0)
-    which = sys.argv[1:] or ["pq", "ste", "pack", "clip", "gptq"]
+    which = sys.argv[1:] or ["pq", "ste", "pack", "clip", "gptq", "qlinear"]
     if "pq" in which:
         gen_pq_int()
     if "ste" in which:
@@ -215,3 +241,5 @@ if __name__ == "__main__":
         gen_clip_autoclip()
     if "gptq" in which:
         gen_gptq()
+    if "qlinear" in which:
+        gen_qlinear()

@@ -60,9 +60,29 @@ def test_autoclip_golden_cases():
         assert bmax.shape == (w.shape[0], w.shape[1] // G, 1) and bmax.dtype == dt
         xs = x[0::x.shape[0] // 512]
         m = _check(w, xs, G, qt, bmax, bmin, idx, err, dt, min_match=0.985)
-        # against the reference's own (T-dtype, noise-limited) choice: its candidate must be close to ours in oracle error
+        # against the REFERENCE's own choice (bmax / bmin stored by make_golden.py from the unmodified auto_2clip_layer):
+        # recover its candidate index from the grid values and compare under the oracle's exact (double) error.
+        #   fp32: the reference's choice IS the exact argmin (measured: 100 %), so ours must agree with it at the same rate
+        #         as with the oracle;
+        #   bf16: the reference's own bf16 contraction is noise-limited (it agrees with the exact argmin in 76-94 % of the
+        #         pairs and lands within 0.7 % of the minimum error); ours must be at least as good as its choice (1e-3)
+        #         and its choice must lie within 1 % of ours.
+        r = oracle.auto_2clip(w, xs, G, 2, qt, want_all_err=True)
+        cmax, cmin = _grid_values(w, G, dt)
+        rmax, rmin = t(c["bmax"], dt).reshape(w.shape[0], -1, 1).float(), t(c["bmin"], dt).reshape(w.shape[0], -1, 1).float()
+        hit_p, hit_n = cmax.float() == rmax, cmin.float() == rmin
+        assert bool(hit_p.any(-1).all() and hit_n.any(-1).all()), "reference clip values are not grid values"
+        ridx = hit_p.float().argmax(-1) * 10 + hit_n.float().argmax(-1)
+        ii = idx.cpu().long().clamp(min=0)
+        e_ref = r["all_err"].gather(-1, ridx[..., None]).squeeze(-1)
+        e_ours = r["all_err"].gather(-1, ii[..., None]).squeeze(-1)
+        assert bool((e_ours <= e_ref * (1 + 1e-3) + 1e-30).all()), (meta, float((e_ours / e_ref).max()))
+        assert bool((e_ref <= e_ours * 1.01 + 1e-30).all()), (meta, float((e_ref / e_ours).max()))
+        ref_match = (ii == ridx).float().mean().item()
+        if dname == "f32":
+            assert ref_match >= 0.985, (meta, ref_match)
         n += 1
-        print(meta, "index match vs oracle", m)
+        print(meta, "index match vs oracle", m, "vs reference's choice", ref_match)
     assert n == 8
 
 

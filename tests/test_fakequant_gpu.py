@@ -84,6 +84,105 @@ def test_ste_quantizers_golden():
     assert bits_equal(y.cpu(), t(z["nan_y"], torch.bfloat16))
 
 
+def _ref_autograd_check(gw, c, w, gy, G, dt, meta):
+    """The CUDA backward against the REFERENCE's own autograd results stored in ste.npz (make_golden.py: `gw` = the
+    reference run in dtype T, `gw64` / `y64` = the same module run in float64), not only against the oracle.
+    (1) vs `gw`: within the T-run's own rounding noise (it accumulates the scale-path sum in T) -- the bound the oracle
+        itself is held to in test_oracle_golden.py.
+    (2) vs `gw64`: in every group where the float64 run took the same codes as the T run (|y - y64| far below one
+        quantisation step), within 2 ulp of T plus the effect of the T-rounded scale on (q - w/s): 1e-7 (fp32) /
+        1e-2 (16-bit) of sum|gy| of the group.  For fp32 this is a tight pin on the closed form."""
+    gw = gw.double().cpu().reshape(-1, G)
+    gs = gy.double().abs().reshape(-1, G).sum(1, keepdim=True)
+    ref_T = t(c["gw"], torch.float64).reshape(-1, G)
+    tol = 8 * ulp_of(ref_T, dt) + 1e-6 if dt != torch.float32 else 1e-4 * (ref_T.abs() + 1.0)
+    noise = {torch.float32: 1e-5, torch.bfloat16: 4e-2, torch.float16: 5e-3}[dt]
+    bad = (gw - ref_T).abs() > tol + noise * gs
+    assert bad.float().mean() < 0.002, (meta, "vs reference T autograd", float(bad.float().mean()))
+    y, y64 = t(c["y"], torch.float64).reshape(-1, G), torch.from_numpy(c["y64"]).reshape(-1, G)
+    wg = w.double().reshape(-1, G)
+    agree = ((y - y64).abs() <= 0.04 * (wg.amax(1, keepdim=True) - wg.amin(1, keepdim=True)) + 1e-12).all(1)
+    g64 = torch.from_numpy(c["gw64"]).reshape(-1, G)
+    noise64 = {torch.float32: 1e-7, torch.bfloat16: 1e-2, torch.float16: 1e-2}[dt]
+    bad = ((gw - g64).abs() > 2.01 * ulp_of(g64, dt) + noise64 * gs + 1e-30)[agree]
+    assert not bool(bad.any()), (meta, "vs reference f64 autograd", int(bad.sum()))
+    return int(agree.sum()), int(agree.numel())
+
+
+def test_ste_backward_vs_reference_autograd():
+    """the stored reference gradients are read by a GPU test."""
+    from bitdistiller_b200.quantizer import SteInt2AsymQuantizer, SteInt3AsymQuantizer, SteN2F3Quantizer
+    n = ag = tot = 0
+    for meta, c in load_cases("ste"):
+        qname, dname, kind, G = meta[0], meta[1], meta[2], int(meta[3])
+        dt = DT[dname]
+        w, gy = t(c["w"], dt), t(c["gy"], dt)
+        mod = {"int2": SteInt2AsymQuantizer, "int3": SteInt3AsymQuantizer, "nf3": SteN2F3Quantizer}[qname](G)
+        x = w.to(dev()).requires_grad_(True)
+        mod(x).backward(gy.to(dev()))
+        a, b = _ref_autograd_check(x.grad, c, w, gy, G, dt, meta)
+        ag, tot, n = ag + a, tot + b, n + 1
+    assert n == 90 and ag > 0.7 * tot  # most groups are checked against the float64 autograd too
+
+
+@pytest.mark.parametrize("dname", ["f32", "bf16", "f16"])
+def test_backward_cuda_semantics(dname, monkeypatch):
+    """the backward under BDQ_SEMANTICS=cuda (the package default), against the oracle's sem=1 closed
+    form AND against eager-PyTorch autograd of the reference formula run on the GPU itself in float64 where codes agree."""
+    from bitdistiller_b200.quantizer import SteInt2AsymQuantizer, SteInt3AsymQuantizer, SteN2F3Quantizer
+    monkeypatch.setenv("BDQ_SEMANTICS", "cuda")
+    dt = DT[dname]
+    w = make_weight("randn", 128, 2048, dt, 17)
+    lim = w.float().reshape(128, -1, 128).abs().amax(-1, keepdim=True) * 0.8
+    w = torch.clamp(w.float().reshape(128, -1, 128), -lim, lim).reshape(128, 2048).to(dt)
+    gy = make_weight("uniform", 128, 2048, dt, 18)
+    for mod, orc in [(SteInt2AsymQuantizer(128), lambda: oracle.int_ste_bwd(w, gy, 128, 2, sem=1)),
+                     (SteInt3AsymQuantizer(128), lambda: oracle.int_ste_bwd(w, gy, 128, 3, sem=1)),
+                     (SteInt2AsymQuantizer(64), lambda: oracle.int_ste_bwd(w, gy, 64, 2, sem=1)),
+                     (SteN2F3Quantizer(128), lambda: oracle.nf3_ste_bwd(w, gy, 128, sem=1))]:
+        x = w.to(dev()).requires_grad_(True)
+        y = mod(x)
+        y.backward(gy.to(dev()))
+        _bwd_check(x.grad, w, gy, mod.q_group_size, orc(), dt, (dname, type(mod).__name__, "sem=cuda"))
+        if isinstance(mod, SteN2F3Quantizer):
+            assert bits_equal(y.detach().cpu(), torch_nf3_fakequant(w.to(dev()), 128).cpu())
+        else:
+            e_dq, _, _ = torch_int_fakequant(w.to(dev()), mod.bit, mod.q_group_size, True)
+            assert bits_equal(y.detach().cpu(), e_dq.cpu()), (dname, type(mod).__name__)
+
+
+def test_bench_launch_shape_vs_oracle():
+    """the launch shape bench.py times -- ONE launch over the flat 202.4 M-weight bf16 buffer of a
+    Llama-2-7B decoder layer (whole-wave grid) -- forward and STE backward against the oracle on sampled slabs
+    (first / last / wave boundaries / random), bit-exact forward, backward within the closed-form bound."""
+    from bitdistiller_b200 import _lib as L
+    G, n = 128, 4 * 4096 * 4096 + 3 * 11008 * 4096
+    gen = torch.Generator(device=dev()).manual_seed(5)
+    w = (torch.randn(n, device=dev(), generator=gen) * 0.02).to(torch.bfloat16)
+    gy = torch.randn(n, device=dev(), generator=gen).to(torch.bfloat16)
+    dq, gw = torch.empty_like(w), torch.empty_like(w)
+    lib, st = L.lib(), L.stream_ptr(dev())
+    L.check(lib.bdq_int_fakequant_fwd(L.ptr(w), L.ptr(dq), None, None, None, None, None, L.i64(n), G, 2, L.BF16,
+                                      L.ROUND_HALF_AWAY, L.SEM_CPU, st), "fwd")
+    L.check(lib.bdq_int_ste_bwd(L.ptr(w), L.ptr(gy), L.ptr(gw), L.i64(n), G, 2, L.BF16, L.SEM_CPU, st), "bwd")
+    slab = 64 * 1024
+    rs = np.random.RandomState(0)
+    starts = [0, n - slab, n // 2 - slab // 2] + [int(s) * G for s in rs.randint(0, (n - slab) // G, size=13)]
+    for s0 in starts:
+        ws, gs = w[s0:s0 + slab].cpu(), gy[s0:s0 + slab].cpu()
+        ref = oracle.int_fakequant(ws, G, 2, round_mode=1)
+        assert bits_equal(dq[s0:s0 + slab].cpu(), ref["dq"].reshape(-1)), s0
+        _bwd_check(gw[s0:s0 + slab], ws, gs, G, oracle.int_ste_bwd(ws, gs, G, 2).reshape(-1), torch.bfloat16, s0)
+    # checksum of the whole buffer against a second, differently shaped launch sequence (per 16 M-element chunk)
+    dq2 = torch.empty_like(w)
+    step = 16 * 1024 * 1024
+    for s0 in range(0, n, step):
+        m = min(step, n - s0)
+        L.check(lib.bdq_int_fakequant_fwd(L.ptr(w[s0:]), L.ptr(dq2[s0:]), None, None, None, None, None, L.i64(m), G, 2,
+                                          L.BF16, L.ROUND_HALF_AWAY, L.SEM_CPU, st), "fwd chunk")
+    assert torch.equal(dq.view(torch.int16), dq2.view(torch.int16))
+
+
 @pytest.mark.parametrize("dname", ["f32", "bf16", "f16"])
 @pytest.mark.parametrize("kind", ["randn", "uniform", "heavy"])
 def test_large_vs_oracle(dname, kind):

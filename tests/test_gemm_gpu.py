@@ -89,3 +89,25 @@ def test_gemm_w2_fallback_shapes():
     out = gemm_w2(x, qw, qs, qz, 128)
     ref, dqw = _ref_gpu(x, qw, qz, qs, 128)
     _check(out, ref, x, dqw)
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs in one process")
+def test_second_device_in_one_process():
+    """MaxDynamicSharedMemorySize is a per-device attribute -- the > 48 KB kernels (tcgen05 GEMM, stream GEMV,
+    autoclip) must also launch on cuda:1 after they ran on cuda:0 in the same process."""
+    from bitdistiller_b200 import awq_inference_engine as E
+    from bitdistiller_b200.autoclip import auto_2clip_layer
+    from bitdistiller_b200.triton_kernels import gemm_w2
+    (qw, qz, qs), dq = _packed_layer(512, 1024, 5)
+    x = torch.randn(256, 1024, generator=torch.Generator().manual_seed(1)).to(torch.float16)
+    w = make_weight("randn", 64, 256, torch.bfloat16, 3)
+    xa = torch.randn(512, 256, generator=torch.Generator().manual_seed(2)).to(torch.bfloat16)
+    outs = []
+    for d in ("cuda:0", "cuda:1"):
+        o = gemm_w2(x.to(d), qw.to(d), qs.to(d), qz.to(d), 128)
+        v = E.gemv_forward_cuda(x[:1].to(d), qw.to(d), qs.to(d), qz.to(d), 2, 128)
+        a, b = auto_2clip_layer(w.to(d), xa.to(d), 2, {"zero_point": True, "q_group_size": 128, "quant_type": "int"})
+        torch.cuda.synchronize(d)
+        outs.append((o.cpu(), v.cpu(), a.cpu(), b.cpu()))
+    for p, q in zip(*outs):
+        assert torch.equal(p, q)

@@ -288,3 +288,75 @@ def test_tp_epilogues_write_own_and_peer_slices():
     L.check(rc, "bdq_gemm_w2_tp")
     assert torch.equal(mine[:, half:], refm[:, half:]) and torch.equal(peer[:, half:], refm[:, half:])
     assert not mine[:, :half].any() and not peer[:, :half].any()
+
+
+def _chain_layers(hidden, kv, inter, layers, silu, seed=0):
+    """A dependent decode chain: q/k/v <- x, o <- q, gate/up <- o, down <- gate (or silu(gate)*up), next layer <- down."""
+    from bitdistiller_b200 import quantizer as Q
+    from bitdistiller_b200.qmodule import pack_wq
+
+    def packed(oc, ic, s):
+        g = torch.Generator(device=dev).manual_seed(s)
+        w = (torch.randn(oc, ic, device=dev, generator=g) * ic ** -0.5).half()
+        dq, sc, z, _ = Q.int_fakequant(w, 2, 128, 0, want_scale_zp=True)
+        qw, qz, qs = pack_wq(dq, sc.view(oc, -1), z.view(oc, -1), 2, 128)
+        return qw, qs, qz, torch.zeros(1, oc, dtype=torch.float16, device=dev)
+
+    x0 = torch.randn(1, hidden, generator=torch.Generator().manual_seed(seed)).half().to(dev)
+    phases, x = [], x0
+    for li in range(layers):
+        q, k, v = packed(hidden, hidden, 10 * li + 1), packed(kv, hidden, 10 * li + 2), packed(kv, hidden, 10 * li + 3)
+        o = packed(hidden, hidden, 10 * li + 4)
+        gt, up = packed(inter, hidden, 10 * li + 5), packed(inter, hidden, 10 * li + 6)
+        dn = packed(hidden, inter, 10 * li + 7)
+        phases.append({"x": x, "mats": [q, k, v], "nowait": li == 0})
+        phases.append({"x": q[3], "mats": [o]})
+        if silu:
+            phases.append({"x": o[3], "mats": [gt, (up[0], up[1], up[2], None)], "silu": True})
+        else:
+            phases.append({"x": o[3], "mats": [gt, up]})
+        phases.append({"x": gt[3], "mats": [dn]})
+        x = dn[3]
+    return phases
+
+
+@pytest.mark.parametrize("hidden,kv,inter,layers,silu", [(1024, 256, 2816, 3, False), (4096, 1024, 12288, 2, False),
+                                                         (512, 128, 1408, 4, True), (4096, 1024, 11008, 1, True)])
+def test_decode_chain_equals_launch_sequence(hidden, kv, inter, layers, silu):
+    """bdq_gemv_w2_chain_* (one persistent launch, grid barriers between dependent phases) is bit-equal to the same phases
+    issued as consecutive bdq_gemv_w2_multi launches; a second run of the same plan (counters reset in-kernel) too."""
+    from bitdistiller_b200 import awq_inference_engine as E
+    phases = _chain_layers(hidden, kv, inter, layers, silu)
+
+    def outs():
+        return [m[3] for ph in phases for m in ph["mats"] if m[3] is not None]
+
+    for ph in phases:   # the reference sequence: one launch per phase
+        mats = ph["mats"]
+        if ph.get("silu"):
+            E.gemv_silu_mul_forward_cuda(ph["x"], mats[0][:3], mats[1][:3], 128, out=mats[0][3])
+        else:
+            E.gemv_multi_forward_cuda(ph["x"], [m[0] for m in mats], [m[1] for m in mats], [m[2] for m in mats], 128,
+                                      outs=[m[3] for m in mats])
+    torch.cuda.synchronize()
+    ref = [o.clone() for o in outs()]
+    assert all(bool(r.isfinite().all()) and float(r.abs().max()) > 0 for r in ref)
+    chain = E.DecodeChain(phases)
+    for rep in range(3):
+        for o in outs():
+            o.zero_()
+        chain.run(lookahead=1 + rep)
+        torch.cuda.synchronize()
+        for i, (a, b) in enumerate(zip(outs(), ref)):
+            assert torch.equal(a, b), (rep, i, float((a.float() - b.float()).abs().max()))
+
+
+def test_decode_chain_errors():
+    from bitdistiller_b200 import _lib as L
+    from bitdistiller_b200 import awq_inference_engine as E
+    phases = _chain_layers(512, 128, 1408, 1, False)
+    bad = [dict(phases[0], x=torch.randn(2, 512, device=dev).half())]
+    with pytest.raises(ValueError):
+        E.DecodeChain(bad)
+    with pytest.raises(L.BdqError):
+        E.DecodeChain([dict(phases[0], x=torch.randn(1, 512).half())])

@@ -114,6 +114,21 @@ def time_fn(fn, iters=20, warm=3):
     return ts[len(ts) // 2] * 1e-3
 
 
+def chain_of(ops):
+    """The same dependent ops as ONE persistent launch (DecodeChain): phases = the fused launch groups."""
+    from bitdistiller_b200.awq_inference_engine import DecodeChain
+    phases = []
+    for gi, (i, n) in enumerate(groups_of(ops, True)):
+        grp = ops[i:i + n]
+        phases.append({"x": grp[0][0], "mats": [(o[1], o[2], o[3], o[4]) for o in grp], "nowait": gi == 0})
+    return DecodeChain(phases)
+
+
+def chain_time(ops, lookahead=2, iters=20):
+    ch = chain_of(ops)
+    return time_fn(lambda: ch.run(lookahead), iters=iters)
+
+
 def graph_time(ops, flags, fused, dev, prefetch=False):
     s = torch.cuda.Stream(dev)
     with torch.cuda.stream(s):
@@ -145,6 +160,9 @@ def main():
                 for pre in ((False, True) if (batch == 1 and vf != RING) else (False,)):
                     key = f"{vname:14s} {'fused(4/layer)' if fused else 'split(7/layer)'} {pname:9s} {'+L2hint' if pre else ''}"
                     res[key] = graph_time(ops, vf | pf, fused, dev, pre)
+    if batch == 1:
+        for la in (1, 2, 3, 4, 6):
+            res[f"persistent chain (1 launch/token) lookahead {la}"] = chain_time(ops, la)
     for k, t in res.items():
         print(f"batch {batch} {k:50s}: {t*1e6:8.1f} us/token  {1/t:8.1f} tok/s  {nbytes/t/1e9:7.1f} GB/s  "
               f"{nbytes/t/1e9/peak*100:5.1f}% of measured HBM peak ({nbytes/1e9:.3f} GB/token)")
