@@ -657,19 +657,14 @@ def secondary_metrics(torch, dev, peak):
     ops = bench_gemv.build(dev, batch=1, chain=True)
     nbytes = bench_gemv.bytes_per_token(ops)
     t_graph = bench_gemv.graph_time(ops, 1, True, dev, True)
-    t_chain, la_best = None, None
-    for la in (2, 3, 4):
-        tc = bench_gemv.chain_time(ops, la)
-        if t_chain is None or tc < t_chain:
-            t_chain, la_best = tc, la
+    t_chain = bench_gemv.chain_time(ops, 0)
     t = min(t_graph, t_chain)
     out["gemv_int2_decode_qwen3_8b"] = {"tok_s": 1.0 / t, "us_per_token": t * 1e6, "bytes_per_token": nbytes,
                                         "frac_of_hbm_peak": nbytes / t / 1e9 / peak,
-                                        "persistent_chain_us_per_token": t_chain * 1e6, "persistent_chain_lookahead": la_best,
+                                        "persistent_chain_us_per_token": t_chain * 1e6,
                                         "graph_pdl_us_per_token": t_graph * 1e6,
-                                        "mode": "best of: ONE persistent launch per token (bdq_gemv_w2_chain: 144 dependent phases, grid "
-                                                "barriers on an L2 counter, weights prefetched HBM -> L2 ahead of the barrier) | CUDA graph "
-                                                "+ PDL with 144 dependent launches"}
+                                        "mode": "best of: CUDA graph + PDL with 144 dependent launches | ONE persistent launch per token "
+                                                "(bdq_gemv_w2_chain: 144 dependent phases separated by grid barriers on an L2 counter)"}
     big = gemv_big.run(dev, peak, 1, shapes=((151936, 4096),))[0]
     out["gemv_int2_kernel_streaming"] = {"shape": [big["OC"], big["IC"]], "mb": big["MB"], "us_per_launch": big["us_per_launch"],
                                          "gbs": big["gbs"], "frac_of_hbm_peak": big["frac_of_hbm_peak"],

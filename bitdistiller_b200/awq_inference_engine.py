@@ -129,15 +129,13 @@ class DecodeChain:
     gemv_multi_forward_cuda / gemv_silu_mul_forward_cuda launches one after the other.  The tensors are referenced by
     address: keep them alive and do not reallocate them."""
 
-    def __init__(self, phases, group_size=128):
+    def __init__(self, phases, group_size=128, max_phases_per_launch=None):
         import ctypes
         if not phases:
             raise ValueError("DecodeChain needs at least one phase")
-        self._keep = []
-        arr = (_Phase * len(phases))()
+        self._keep, self._runs = [], []
         dev = phases[0]["x"].device
-        self.max_ic = 0
-        for p, ph in enumerate(phases):
+        for ph in phases:
             x, mats = ph["x"], ph["mats"]
             L.require_cuda(x, *[t for m in mats for t in m if t is not None])
             _check_fp16(x, *[m[1] for m in mats])
@@ -145,29 +143,40 @@ class DecodeChain:
                 raise ValueError("DecodeChain is the batch-1 decode path: every x must hold one contiguous row")
             if not 1 <= len(mats) <= 4:
                 raise ValueError("a phase takes 1..4 matrices")
-            a = arr[p]
-            a.x, a.nmat, a.group, a.IC = x.data_ptr(), len(mats), int(group_size), x.shape[-1]
-            a.flags = (GEMV_SILU_MUL if ph.get("silu") else 0) | (GEMV_CHAIN_NOWAIT if ph.get("nowait") else 0)
-            for i, (qw, sc, qz, out) in enumerate(mats):
-                assert qw.is_contiguous() and sc.is_contiguous() and qz.is_contiguous() and qw.shape[1] * 16 == x.shape[-1]
-                a.qweight[i], a.scales[i], a.qzeros[i] = qw.data_ptr(), sc.data_ptr(), qz.data_ptr()
-                a.out[i] = 0 if out is None else out.data_ptr()
-                a.OC[i] = qw.shape[0]
-                self._keep += [qw, sc, qz, out]
-            self._keep.append(x)
-            self.max_ic = max(self.max_ic, x.shape[-1])
         self.n, self.device = len(phases), dev
+        self.max_ic = max(ph["x"].shape[-1] for ph in phases)
         lib = L.lib()
         lib.bdq_gemv_w2_chain_workspace_bytes.restype = ctypes.c_int64
-        nbytes = int(lib.bdq_gemv_w2_chain_workspace_bytes(self.n))
-        self.workspace = torch.zeros(nbytes + 256, dtype=torch.uint8, device=dev)
-        off = (-self.workspace.data_ptr()) % 256
-        self._ws = ctypes.c_void_p(self.workspace.data_ptr() + off)
-        with torch.cuda.device(dev):
-            rc = lib.bdq_gemv_w2_chain_prepare(arr, self.n, self._ws, L.i64(nbytes), L.stream_ptr(dev))
-        L.check(rc, "bdq_gemv_w2_chain_prepare")
+        cap = int(lib.bdq_gemv_w2_chain_max_phases(L.i64(self.max_ic)))
+        if cap < 1:
+            raise L.BdqError(f"DecodeChain: in_features {self.max_ic} do not fit the persistent kernel's shared memory")
+        if max_phases_per_launch:
+            cap = max(1, min(cap, int(max_phases_per_launch)))
+        # one launch holds `cap` phases (the plan lives in shared memory): longer chains run as consecutive launches
+        for s0 in range(0, self.n, cap):
+            sub = phases[s0:s0 + cap]
+            arr = (_Phase * len(sub))()
+            for a, ph in zip(arr, sub):
+                x, mats = ph["x"], ph["mats"]
+                a.x, a.nmat, a.group, a.IC = x.data_ptr(), len(mats), int(group_size), x.shape[-1]
+                a.flags = (GEMV_SILU_MUL if ph.get("silu") else 0) | (GEMV_CHAIN_NOWAIT if ph.get("nowait") else 0)
+                for i, (qw, sc, qz, out) in enumerate(mats):
+                    assert qw.is_contiguous() and sc.is_contiguous() and qz.is_contiguous() and qw.shape[1] * 16 == x.shape[-1]
+                    a.qweight[i], a.scales[i], a.qzeros[i] = qw.data_ptr(), sc.data_ptr(), qz.data_ptr()
+                    a.out[i] = 0 if out is None else out.data_ptr()
+                    a.OC[i] = qw.shape[0]
+                    self._keep += [qw, sc, qz, out]
+                self._keep.append(x)
+            nbytes = int(lib.bdq_gemv_w2_chain_workspace_bytes(len(sub)))
+            ws = torch.zeros(nbytes + 256, dtype=torch.uint8, device=dev)
+            ptr = ctypes.c_void_p(ws.data_ptr() + (-ws.data_ptr()) % 256)
+            with torch.cuda.device(dev):
+                rc = lib.bdq_gemv_w2_chain_prepare(arr, len(sub), ptr, L.i64(nbytes), L.stream_ptr(dev))
+            L.check(rc, "bdq_gemv_w2_chain_prepare")
+            self._runs.append((ws, ptr, len(sub)))
 
-    def run(self, lookahead=2):
+    def run(self, lookahead=0):
         with torch.cuda.device(self.device):
-            rc = L.lib().bdq_gemv_w2_chain_run(self._ws, self.n, L.i64(self.max_ic), int(lookahead), L.stream_ptr(self.device))
-        L.check(rc, "bdq_gemv_w2_chain_run")
+            for _, ptr, n in self._runs:
+                rc = L.lib().bdq_gemv_w2_chain_run(ptr, n, L.i64(self.max_ic), int(lookahead), L.stream_ptr(self.device))
+                L.check(rc, "bdq_gemv_w2_chain_run")

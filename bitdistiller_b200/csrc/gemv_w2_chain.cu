@@ -9,12 +9,14 @@
 // reduction + exit: profiles/r01_gemv_latency.md), 144 x 3 us = 430 of 690 us per Qwen3-8B token.  Here
 //   * 2 x 148 CTAs stay resident for the whole token and walk a device-side list of phases;
 //   * the dependency between phases is a grid barrier on an L2 counter (one red.release.gpu per CTA after its stores,
-//     one ld.acquire.gpu poller per CTA): ~0.4 us instead of a launch boundary;
-//   * the weights do not depend on x: one lane per CTA keeps `lookahead` phases of packed weights flowing HBM -> L2 with
-//     cp.async.bulk.prefetch.L2 while the CTAs wait / stage x, so HBM streams across the barriers and the register
-//     pipeline of the consumer (the bdq_gemv_w2_multi inner loop: LDG.256 per lane, INT8 digit-plane MMAs) reads L2 hits;
-//   * the first items of a phase are requested BEFORE the barrier wait.
-// Every byte still crosses HBM exactly once per token.
+//     one ld.acquire.gpu poller per CTA) instead of a launch boundary;
+//   * the weights do not depend on x: the register pipeline of the consumer (the bdq_gemv_w2_multi inner loop: LDG.256 per
+//     lane, kDepth items = 6 KB per warp, INT8 digit-plane MMAs) has its own cursor that runs on into the following phases, so
+//     the first items of phase p + 1 are in flight while phase p is reduced, stored and signalled and while the CTA waits;
+//   * the whole plan lives in shared memory (256 B per phase): a phase change costs no dependent global load.
+// An explicit HBM -> L2 prefetch (cp.async.bulk.prefetch.L2 of the next phases, first version of this file) made the token
+// SLOWER (1014 vs 852 us: the prefetch requests queue in front of the demand loads, profiles/r02_chain_timeline.md) and was
+// removed.  Every byte crosses HBM exactly once per token.
 #include <cuda.h>
 #include <cstring>
 
@@ -98,138 +100,214 @@ __device__ __forceinline__ void prefetch_l2(const uint8_t* base, unsigned int nb
 }
 
 __host__ __device__ inline int warp_bytes(int wpw) { return wpw * kWinStride + kZeroBytes; }
-__host__ __device__ inline int smem_bytes(int wpw) { return kWarps * warp_bytes(wpw) + kRedSlots * kWarps * 64 * 4 + 2 * kDescWords * 4; }
+// [n_phases] plan copy | [8 warps] x windows + zero block | red
+__host__ __device__ inline int smem_bytes(int wpw, int n_phases) {
+    return n_phases * (int)sizeof(Phase) + kWarps * warp_bytes(wpw) + kRedSlots * kWarps * 64 * 4;
+}
 
 // counters: [n_phases] arrivals per phase, then [n_phases] = CTAs done with the whole chain (reset by the last one)
+//
+// Structure: ONE flat loop over this warp's items of ALL phases.  The producer side (register pipeline of kDepth items,
+// LDG.256 per lane) has its own phase cursor and simply keeps going into the next phases -- the weights do not depend on
+// x -- so the first items of phase p + 1 are in flight while phase p is still being consumed, reduced and signalled.
+// The consumer side crosses a phase boundary with: flush + split-K reduction + stores, one CTA barrier, one
+// red.release.gpu on the phase counter, [poll the counter of the phase it depends on], stage x.
 __global__ void __launch_bounds__(kThreads, 2) gemv_w2_chain_kernel(const Phase* __restrict__ plan, int n_phases, int wpw_max,
-                                                                     unsigned int* __restrict__ counters, int lookahead) {
+                                                                     unsigned int* __restrict__ counters, int lookahead,
+                                                                     unsigned long long* __restrict__ prof, int dbg) {
     extern __shared__ __align__(128) uint8_t smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int g = lane >> 2, t = lane & 3;
     const int ncta = (int)gridDim.x, cta = (int)blockIdx.x;
-    uint8_t* wbase = smem + (size_t)warp * warp_bytes(wpw_max);
+    const Phase* splan = reinterpret_cast<const Phase*>(smem);
+    uint8_t* wbase = smem + (size_t)n_phases * sizeof(Phase) + (size_t)warp * warp_bytes(wpw_max);
     uint8_t* zblock = wbase + (size_t)wpw_max * kWinStride;
-    float* red = reinterpret_cast<float*>(smem + (size_t)kWarps * warp_bytes(wpw_max));
-    uint32_t* sdesc = reinterpret_cast<uint32_t*>(red + kRedSlots * kWarps * 64);   // [2][kDescWords]
+    float* red = reinterpret_cast<float*>(smem + (size_t)n_phases * sizeof(Phase) + (size_t)kWarps * warp_bytes(wpw_max));
 
     for (int i = lane; i < kZeroBytes / 16; i += 32) reinterpret_cast<uint4*>(zblock)[i] = make_uint4(0, 0, 0, 0);
-    if (tid < kDescWords) sdesc[tid] = reinterpret_cast<const uint32_t*>(plan)[tid];
-    // HBM -> L2 for the first `lookahead` phases (phase p + lookahead is requested when phase p starts)
-    if (tid == kThreads - 1) {
-        for (int q = 0; q < lookahead && q < n_phases; ++q) {
-            const Phase* P = plan + q;
-            for (int i = 0; i < P->nmat; ++i) {
-                prefetch_l2(P->qw[i], P->qw_bytes[i], cta, ncta);
-                prefetch_l2(reinterpret_cast<const uint8_t*>(P->sc[i]), P->sc_bytes[i], cta, ncta);
-                prefetch_l2(reinterpret_cast<const uint8_t*>(P->qz[i]), P->qz_bytes[i], cta, ncta);
-            }
-        }
-    }
+    for (int i = tid; i < n_phases * (int)(sizeof(Phase) / 16); i += kThreads)
+        reinterpret_cast<uint4*>(smem)[i] = reinterpret_cast<const uint4*>(plan)[i];
     __syncthreads();
 
-    for (int p = 0; p < n_phases; ++p) {
-        const Phase& D = *reinterpret_cast<const Phase*>(sdesc + (p & 1) * kDescWords);
-        uint32_t next_word = 0;
-        if (tid < kDescWords && p + 1 < n_phases) next_word = reinterpret_cast<const uint32_t*>(plan + p + 1)[tid];
-        const int IC = D.IC, zw = D.zw, silu = D.silu;
-        const int ngrp = IC >> 7, nwin = (ngrp + 3) >> 2;
-        const int row_bytes = IC >> 2, zw16 = zw * 16;
-        const int rb_u = silu ? 2 : 1;
-        const int rb0 = (cta * D.rb_q + min(cta, D.rb_r)) * rb_u;
-        const int rb1 = rb0 + (D.rb_q + (cta < D.rb_r ? 1 : 0)) * rb_u;
-        auto mat_of = [&](int rb) {
-            if (silu) return rb & 1;
-            int mi = 0;
-            while (mi < kMaxMats - 1 && rb >= D.rb_end[mi]) ++mi;
-            return mi;
-        };
-        auto rstart_of = [&](int mi) { return mi ? D.rb_end[mi - 1] : 0; };
-        auto blk_of = [&](int rb, int mi) { return silu ? (rb >> 1) : rb - rstart_of(mi); };
-        const int mywin = warp < nwin ? (nwin - warp + kWarps - 1) / kWarps : 0;
+    // dev tool: %globaltimer marks of thread 0 of every CTA, prof[(cta * n_phases + p) * 8 + slot]
+    auto mark = [&](int p, int slot) {
+        if (prof && tid == 0) {
+            unsigned long long v;
+            asm volatile("mov.u64 %0, %globaltimer;" : "=l"(v));
+            prof[((size_t)cta * n_phases + p) * 8 + slot] = v;
+        }
+    };
+    auto rb_range = [&](const Phase& P, int& r0, int& r1) {
+        const int rb_u = P.silu ? 2 : 1;
+        r0 = (cta * P.rb_q + min(cta, P.rb_r)) * rb_u;
+        r1 = r0 + (P.rb_q + (cta < P.rb_r ? 1 : 0)) * rb_u;
+    };
+    auto mat_of = [&](const Phase& P, int rb) {
+        if (P.silu) return rb & 1;
+        int mi = 0;
+        while (mi < kMaxMats - 1 && rb >= P.rb_end[mi]) ++mi;
+        return mi;
+    };
+    auto blk_of = [&](const Phase& P, int rb, int mi) { return P.silu ? (rb >> 1) : rb - (mi ? P.rb_end[mi - 1] : 0); };
+    auto mywin_of = [&](const Phase& P) {
+        const int nwin = ((P.IC >> 7) + 3) >> 2;
+        return warp < nwin ? (nwin - warp + kWarps - 1) / kWarps : 0;
+    };
 
-        // ---- producer cursor (register pipeline of kDepth items, see gemv_w2_stream.cu)
-        int p_rb = rb0, p_j = 0, p_mi = mat_of(rb0);
-        const int G0 = 4 * warp + t;
-        const uint8_t* pa0 = nullptr;
-        const __half* ps0 = nullptr;
-        const uint32_t* pz0 = nullptr;
-        auto set_base = [&]() {
-            const size_t r = (size_t)blk_of(p_rb, p_mi) * 16 + g;
-            pa0 = D.qw[p_mi] + r * row_bytes + (size_t)G0 * 32;
-            ps0 = D.sc[p_mi] + r * zw16 + G0;
-            pz0 = D.qz[p_mi] + r * zw + (G0 >> 4);
-        };
-        if (rb0 < rb1) set_base();
-        auto issue = [&](ItemBuf& b) {
-            if (p_rb >= rb1) return;
-            if (G0 + 32 * p_j < ngrp) {
-                const uint8_t* pa = pa0 + p_j * 1024;
-                b.a = ldg256(pa);
-                b.b = ldg256(pa + (size_t)8 * row_bytes);
-            } else {
-#pragma unroll
-                for (int i = 0; i < 8; ++i) b.a.r[i] = b.b.r[i] = 0u;
+    // ---------------------------------------------------------------- producer: cursor over (phase, block, window)
+    const int G0 = 4 * warp + t;
+    int q_p = -1, q_rb = 0, q_rb1 = 0, q_j = 0, q_mi = 0, q_mywin = 0, q_ngrp = 0, q_rowb = 0, q_zw = 0;
+    const uint8_t* pa0 = nullptr;
+    const __half* ps0 = nullptr;
+    const uint32_t* pz0 = nullptr;
+    auto q_set_base = [&]() {
+        const Phase& P = splan[q_p];
+        const size_t r = (size_t)blk_of(P, q_rb, q_mi) * 16 + g;
+        pa0 = P.qw[q_mi] + r * q_rowb + (size_t)G0 * 32;
+        ps0 = P.sc[q_mi] + r * (q_zw * 16) + G0;
+        pz0 = P.qz[q_mi] + r * q_zw + (G0 >> 4);
+    };
+    auto q_next_phase = [&]() {   // move to the next phase in which this warp has items; false at the end of the chain
+        while (++q_p < n_phases) {
+            const Phase& P = splan[q_p];
+            q_mywin = mywin_of(P);
+            rb_range(P, q_rb, q_rb1);
+            if (q_mywin > 0 && q_rb < q_rb1) {
+                q_ngrp = P.IC >> 7;
+                q_rowb = P.IC >> 2;
+                q_zw = P.zw;
+                q_j = 0;
+                q_mi = mat_of(P, q_rb);
+                q_set_base();
+                return true;
             }
-            const __half* ps = ps0 + 32 * p_j;
-            b.sa = ldg_nc_u16(ps);
-            b.sb = ldg_nc_u16(ps + (size_t)8 * zw16);
-            const uint32_t* pz = pz0 + 2 * p_j;
-            b.za = ldg_nc_u32(pz);
-            b.zb = ldg_nc_u32(pz + (size_t)8 * zw);
-            if (++p_j == mywin) {
-                p_j = 0;
-                ++p_rb;
-                if (silu || p_rb >= D.rb_end[p_mi]) {
-                    p_mi = mat_of(p_rb);
-                    if (p_rb < rb1) set_base();
+        }
+        q_p = n_phases;
+        return false;
+    };
+    auto issue = [&](ItemBuf& b) {
+        if (q_p >= n_phases) return;
+        if (G0 + 32 * q_j < q_ngrp) {
+            const uint8_t* pa = pa0 + q_j * 1024;
+            b.a = ldg256(pa);
+            b.b = ldg256(pa + (size_t)8 * q_rowb);
+        } else {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) b.a.r[i] = b.b.r[i] = 0u;
+        }
+        const __half* ps = ps0 + 32 * q_j;
+        b.sa = ldg_nc_u16(ps);
+        b.sb = ldg_nc_u16(ps + (size_t)8 * (q_zw * 16));
+        const uint32_t* pz = pz0 + 2 * q_j;
+        b.za = ldg_nc_u32(pz);
+        b.zb = ldg_nc_u32(pz + (size_t)8 * q_zw);
+        if (++q_j == q_mywin) {
+            q_j = 0;
+            if (++q_rb >= q_rb1) {
+                q_next_phase();
+            } else {
+                const Phase& P = splan[q_p];
+                if (P.silu || q_rb >= P.rb_end[q_mi]) {
+                    q_mi = mat_of(P, q_rb);
+                    q_set_base();
                 } else {
-                    pa0 += (size_t)16 * row_bytes;
-                    ps0 += (size_t)16 * zw16;
-                    pz0 += (size_t)16 * zw;
+                    pa0 += (size_t)16 * q_rowb;
+                    ps0 += (size_t)16 * (q_zw * 16);
+                    pz0 += (size_t)16 * q_zw;
                 }
             }
-        };
-        ItemBuf buf[kDepth];
-        if (mywin > 0) {
+        }
+    };
+
+    // ---------------------------------------------------------------- consumer state
+    int p = 0;                         // phase being consumed (CTA-uniform)
+    int c_left = 0, c_j = 0, c_mywin = 0, rslot = 0, rb_base = 0, c_rb1 = 0;
+    float fin_lo = 0.f, fin_hi = 0.f;
+    const bool active = ((g >> 1) == t);
+    const uint8_t* bbase = active ? wbase + g * kSlotStride : zblock;
+    const int jstride = active ? kWinStride : 0;
+
+    auto block_reduce = [&]() {
+        const Phase& D = splan[p];
+        __syncthreads();
+        if (tid < rslot * 16) {
+            const int sl = tid >> 4, row = tid & 15;
+            const float* rp = red + sl * kWarps * 64 + row;
+            float acc = 0.f;   // same serial order as bdq_gemv_w2_multi: the chain is bit-equal to the launch sequence
 #pragma unroll
-            for (int d = 0; d < kDepth; ++d) issue(buf[d]);   // nothing here depends on the previous phase
-        }
-        // keep HBM streaming: request phase p + lookahead into L2 (one lane per CTA, its slice of every tensor)
-        if (tid == kThreads - 1 && p + lookahead < n_phases) {
-            const Phase* P = plan + p + lookahead;
-            const int nm = P->nmat;
-            for (int i = 0; i < nm; ++i) {
-                prefetch_l2(P->qw[i], P->qw_bytes[i], cta, ncta);
-                prefetch_l2(reinterpret_cast<const uint8_t*>(P->sc[i]), P->sc_bytes[i], cta, ncta);
-                prefetch_l2(reinterpret_cast<const uint8_t*>(P->qz[i]), P->qz_bytes[i], cta, ncta);
+            for (int w = 0; w < kWarps * 4; ++w) acc += rp[w * 16];
+            const int rb = rb_base + sl;
+            const int mi = mat_of(D, rb);
+            __half hv = __float2half_rn(acc);
+            bool store = true;
+            if (D.silu) {
+                const float up = __shfl_down_sync(0xffffffffu, __half2float(hv), 16);
+                const float gt = __half2float(hv);
+                const float sg = __half2float(__float2half_rn(gt / (1.f + __expf(-gt))));
+                hv = __float2half_rn(sg * up);
+                store = (sl & 1) == 0;
             }
+            const size_t oi = (size_t)blk_of(D, rb, mi) * 16 + row;
+            if (store) D.out[mi][oi] = hv;
         }
-
-        // ---- dependency: every CTA has stored its outputs of phase p - 1
-        if (D.wait && p > 0) {
-            if (tid == 0) {
-                const unsigned int* c = counters + (p - 1);
-                while (ld_acquire_u32(c) < (unsigned int)ncta) {}
-            }
-            __syncthreads();
+        rb_base += rslot;
+        rslot = 0;
+        if (rb_base < c_rb1) __syncthreads();
+    };
+    auto flush = [&]() {
+        float* my = red + ((rslot * kWarps + warp) * 4 + t) * 16;
+        my[g] = fin_lo;
+        my[g + 8] = fin_hi;
+        fin_lo = fin_hi = 0.f;
+        if (++rslot == kRedSlots) block_reduce();
+    };
+    auto consume = [&](const ItemBuf& b) {
+        const uint8_t* bp = bbase + (size_t)c_j * jstride;
+        int acc[4][4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) acc[i][0] = acc[i][1] = acc[i][2] = acc[i][3] = 0;
+#pragma unroll
+        for (int p2 = 0; p2 < 4; ++p2) {
+            const uint4 q0 = *reinterpret_cast<const uint4*>(bp + p2 * 32);
+            const uint4 q1 = *reinterpret_cast<const uint4*>(bp + p2 * 32 + 16);
+            const uint32_t a0 = b.a.r[2 * p2], a1 = b.b.r[2 * p2], a2 = b.a.r[2 * p2 + 1], a3 = b.b.r[2 * p2 + 1];
+            imma16832(acc[0], a0 & 0x03030303u, a1 & 0x03030303u, a2 & 0x03030303u, a3 & 0x03030303u, q0.x, q0.y);
+            imma16832(acc[1], a0 & 0x0C0C0C0Cu, a1 & 0x0C0C0C0Cu, a2 & 0x0C0C0C0Cu, a3 & 0x0C0C0C0Cu, q0.z, q0.w);
+            imma16832(acc[2], a0 & 0x30303030u, a1 & 0x30303030u, a2 & 0x30303030u, a3 & 0x30303030u, q1.x, q1.y);
+            imma16832(acc[3], a0 & 0xC0C0C0C0u, a1 & 0xC0C0C0C0u, a2 & 0xC0C0C0C0u, a3 & 0xC0C0C0C0u, q1.z, q1.w);
         }
+        const float2 mt = *reinterpret_cast<const float2*>(wbase + (size_t)c_j * kWinStride + kMetaOff + t * 8);
+        const int sq64 = __float_as_int(mt.y);
+        const int sh = ((4 * (warp + kWarps * c_j) + t) & 15) * 2;
+        const int za = (int)((b.za >> sh) & 3u), zb = (int)((b.zb >> sh) & 3u);
+        int u[4];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) u[c] = ((acc[0][c] * 4 + acc[1][c]) * 4 + acc[2][c]) * 4 + acc[3][c];
+        const int wa = u[0] * 256 + u[1] - za * sq64, wb = u[2] * 256 + u[3] - zb * sq64;
+        const float sa = __half2float(__ushort_as_half((unsigned short)b.sa)) * mt.x;
+        const float sb = __half2float(__ushort_as_half((unsigned short)b.sb)) * mt.x;
+        fin_lo = fmaf(sa, (float)wa, fin_lo);
+        fin_hi = fmaf(sb, (float)wb, fin_hi);
+    };
 
-        // ---- stage this warp's windows of x as block fixed point (two int8 limbs per activation), see gemv_w2_stream.cu
+    // stage this warp's windows of x as block fixed point (two int8 limbs per activation), see gemv_w2_stream.cu
+    auto stage_x = [&](const Phase& D) {
         const __half* x = D.x;
-        for (int j0 = 0; j0 < mywin; j0 += 4) {
+        const int IC = D.IC;
+        for (int j0 = 0; j0 < c_mywin; j0 += 4) {
             uint4 raw[4][2];
 #pragma unroll
             for (int jj = 0; jj < 4; ++jj) {
                 const int k0 = (warp + kWarps * (j0 + jj)) * 512 + lane * 16;
                 raw[jj][0] = raw[jj][1] = make_uint4(0, 0, 0, 0);
-                if (j0 + jj < mywin && k0 < IC) {
+                if (j0 + jj < c_mywin && k0 < IC) {
                     raw[jj][0] = ld_cg_v4(x + k0);
                     raw[jj][1] = ld_cg_v4(x + k0 + 8);
                 }
             }
 #pragma unroll
             for (int jj = 0; jj < 4; ++jj) {
-                if (j0 + jj >= mywin) break;
+                if (j0 + jj >= c_mywin) break;
                 const uint32_t in[8] = {raw[jj][0].x, raw[jj][0].y, raw[jj][0].z, raw[jj][0].w,
                                         raw[jj][1].x, raw[jj][1].y, raw[jj][1].z, raw[jj][1].w};
                 __half2 m2 = __habs2(*reinterpret_cast<const __half2*>(&in[0]));
@@ -240,9 +318,9 @@ __global__ void __launch_bounds__(kThreads, 2) gemv_w2_chain_kernel(const Phase*
 #pragma unroll
                 for (int sft = 1; sft < 8; sft <<= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, sft));
                 const uint32_t ex = (mx >> 10) & 31u;
-                const uint32_t exc = ex < 1u ? 1u : ex;
-                const float inv_unit = __uint_as_float((154u - exc) << 23);
-                const float unit = ex == 31u ? __uint_as_float(0x7fc00000u) : __uint_as_float((exc + 100u) << 23);
+                const float gm = fmaxf(__half2float(__ushort_as_half((unsigned short)mx)), 5.9604645e-8f);   // group max |x| (exact)
+                const float inv_unit = __fdividef(32512.f, gm);
+                const float unit = ex == 31u ? __uint_as_float(0x7fc00000u) : gm * (1.f / 32512.f);
                 uint32_t bits[16], qsum = 0;
 #pragma unroll
                 for (int e = 0; e < 8; ++e) {
@@ -275,103 +353,64 @@ __global__ void __launch_bounds__(kThreads, 2) gemv_w2_chain_kernel(const Phase*
             }
         }
         __syncwarp();
+    };
 
-        // ---- consumer
-        const bool active = ((g >> 1) == t);
-        const uint8_t* bbase = active ? wbase + g * kSlotStride : zblock;
-        const int jstride = active ? kWinStride : 0;
-        float fin_lo = 0.f, fin_hi = 0.f;
-        int c_j = 0, rslot = 0, rb_base = rb0;
-        auto block_reduce = [&]() {
+    // wait for the dependency of phase p, stage x, set the consumer counters
+    auto begin_phase = [&]() {
+        const Phase& D = splan[p];
+        mark(p, 0);
+        int r0;
+        rb_range(D, r0, c_rb1);
+        c_mywin = mywin_of(D);
+        rb_base = r0;
+        rslot = 0;
+        c_j = 0;
+        c_left = (c_rb1 - r0) * c_mywin;
+        if (D.wait && p > 0 && !(dbg & 1)) {
+            if (tid == 0) {
+                const unsigned int* c = counters + (p - 1);
+                while (ld_acquire_u32(c) < (unsigned int)ncta) {}
+            }
             __syncthreads();
-            if (tid < rslot * 16) {
-                const int sl = tid >> 4, row = tid & 15;
-                const float* rp = red + sl * kWarps * 64 + row;
-                float acc = 0.f;
-#pragma unroll
-                for (int w = 0; w < kWarps * 4; ++w) acc += rp[w * 16];
-                const int rb = rb_base + sl;
-                const int mi = mat_of(rb);
-                __half hv = __float2half_rn(acc);
-                bool store = true;
-                if (silu) {
-                    const float up = __shfl_down_sync(0xffffffffu, __half2float(hv), 16);
-                    const float gt = __half2float(hv);
-                    const float sg = __half2float(__float2half_rn(gt / (1.f + __expf(-gt))));
-                    hv = __float2half_rn(sg * up);
-                    store = (sl & 1) == 0;
-                }
-                const size_t oi = (size_t)blk_of(rb, mi) * 16 + row;
-                if (store) D.out[mi][oi] = hv;
-            }
-            rb_base += rslot;
-            rslot = 0;
-            if (rb_base < rb1) __syncthreads();
-        };
-        auto flush = [&]() {
-            float* my = red + ((rslot * kWarps + warp) * 4 + t) * 16;
-            my[g] = fin_lo;
-            my[g + 8] = fin_hi;
-            fin_lo = fin_hi = 0.f;
-            if (++rslot == kRedSlots) block_reduce();
-        };
-        auto consume = [&](const ItemBuf& b) {
-            const uint8_t* bp = bbase + (size_t)c_j * jstride;
-            int acc[4][4];
-#pragma unroll
-            for (int i = 0; i < 4; ++i) acc[i][0] = acc[i][1] = acc[i][2] = acc[i][3] = 0;
-#pragma unroll
-            for (int p2 = 0; p2 < 4; ++p2) {
-                const uint4 q0 = *reinterpret_cast<const uint4*>(bp + p2 * 32);
-                const uint4 q1 = *reinterpret_cast<const uint4*>(bp + p2 * 32 + 16);
-                const uint32_t a0 = b.a.r[2 * p2], a1 = b.b.r[2 * p2], a2 = b.a.r[2 * p2 + 1], a3 = b.b.r[2 * p2 + 1];
-                imma16832(acc[0], a0 & 0x03030303u, a1 & 0x03030303u, a2 & 0x03030303u, a3 & 0x03030303u, q0.x, q0.y);
-                imma16832(acc[1], a0 & 0x0C0C0C0Cu, a1 & 0x0C0C0C0Cu, a2 & 0x0C0C0C0Cu, a3 & 0x0C0C0C0Cu, q0.z, q0.w);
-                imma16832(acc[2], a0 & 0x30303030u, a1 & 0x30303030u, a2 & 0x30303030u, a3 & 0x30303030u, q1.x, q1.y);
-                imma16832(acc[3], a0 & 0xC0C0C0C0u, a1 & 0xC0C0C0C0u, a2 & 0xC0C0C0C0u, a3 & 0xC0C0C0C0u, q1.z, q1.w);
-            }
-            const float2 mt = *reinterpret_cast<const float2*>(wbase + (size_t)c_j * kWinStride + kMetaOff + t * 8);
-            const int sq64 = __float_as_int(mt.y);
-            const int sh = ((4 * (warp + kWarps * c_j) + t) & 15) * 2;
-            const int za = (int)((b.za >> sh) & 3u), zb = (int)((b.zb >> sh) & 3u);
-            int u[4];
-#pragma unroll
-            for (int c = 0; c < 4; ++c) u[c] = ((acc[0][c] * 4 + acc[1][c]) * 4 + acc[2][c]) * 4 + acc[3][c];
-            const int wa = u[0] * 256 + u[1] - za * sq64, wb = u[2] * 256 + u[3] - zb * sq64;
-            const float sa = __half2float(__ushort_as_half((unsigned short)b.sa)) * mt.x;
-            const float sb = __half2float(__ushort_as_half((unsigned short)b.sb)) * mt.x;
-            fin_lo = fmaf(sa, (float)wa, fin_lo);
-            fin_hi = fmaf(sb, (float)wb, fin_hi);
-        };
-
-        if (mywin == 0) {
-            for (int rb = rb0; rb < rb1; ++rb) flush();
-        } else {
-            const int nitems = (rb1 - rb0) * mywin;
-            for (int i = 0; i < nitems; i += kDepth) {
-#pragma unroll
-                for (int d = 0; d < kDepth; ++d) {
-                    if (i + d < nitems) {
-                        consume(buf[d]);
-                        issue(buf[d]);
-                        if (++c_j == mywin) {
-                            c_j = 0;
-                            flush();
-                        }
-                    }
-                }
-            }
         }
+        mark(p, 2);
+        stage_x(D);
+        mark(p, 3);
+        if (c_mywin == 0)   // IC < 4096: this warp owns no window but still takes part in the block reductions
+            for (int rb = r0; rb < c_rb1; ++rb) flush();
+    };
+    // all items of phase p consumed: reduce what is parked, publish
+    auto end_phase = [&]() {
         if (rslot) block_reduce();
+        mark(p, 4);
+        __syncthreads();                           // every thread's stores of this phase precede ...
+        if (tid == 0) red_release_add(counters + p, 1u);   // ... this gpu-scope release (cumulative over the CTA barrier)
+        mark(p, 5);
+    };
 
-        // ---- phase done for this CTA: publish (stores of all threads -> CTA barrier -> one gpu-scope release)
-        __syncthreads();
-        if (tid == 0) {
-            __threadfence();
-            red_release_add(counters + p, 1u);
+    ItemBuf buf[kDepth];
+    q_next_phase();
+#pragma unroll
+    for (int d = 0; d < kDepth; ++d) issue(buf[d]);
+    begin_phase();
+    bool done = false;
+    while (!done) {
+#pragma unroll
+        for (int d = 0; d < kDepth; ++d) {
+            while (c_left == 0) {
+                end_phase();
+                if (++p >= n_phases) { done = true; break; }
+                begin_phase();
+            }
+            if (done) break;
+            consume(buf[d]);
+            issue(buf[d]);
+            --c_left;
+            if (++c_j == c_mywin) {
+                c_j = 0;
+                flush();
+            }
         }
-        if (tid < kDescWords) sdesc[((p + 1) & 1) * kDescWords + tid] = next_word;
-        __syncthreads();
     }
 
     // the last CTA out resets the counters for the next token (every CTA has passed all of its waits by then)
@@ -383,12 +422,31 @@ __global__ void __launch_bounds__(kThreads, 2) gemv_w2_chain_kernel(const Phase*
             __threadfence();
         }
     }
+    (void)lookahead;
 }
 
 }  // namespace chain
 }  // namespace bdq
 
 using namespace bdq;
+
+static unsigned long long* g_chain_prof = nullptr;
+static int64_t g_chain_prof_cap = 0;
+// dev tool: device buffer of `cap` u64; every later run writes [grid][n_phases][8] %globaltimer marks into it
+extern "C" int bdq_gemv_w2_chain_set_prof(void* buf, int64_t cap) {
+    g_chain_prof = (unsigned long long*)buf;
+    g_chain_prof_cap = cap;
+    return BDQ_OK;
+}
+
+// phases one run can hold (the plan is copied into shared memory next to the x windows; two CTAs per SM)
+extern "C" int bdq_gemv_w2_chain_max_phases(int64_t max_IC) {
+    if (max_IC <= 0 || max_IC % 128 != 0) return 0;
+    const int nwin = (int)((max_IC / 128 + 3) / 4);
+    const int wpw = (nwin + chain::kWarps - 1) / chain::kWarps;
+    const int fixed = chain::smem_bytes(wpw, 0);
+    return fixed >= 112 * 1024 ? 0 : (112 * 1024 - fixed) / (int)sizeof(chain::Phase);
+}
 
 extern "C" int64_t bdq_gemv_w2_chain_workspace_bytes(int n_phases) {
     if (n_phases < 1) return 0;
@@ -470,8 +528,12 @@ extern "C" int bdq_gemv_w2_chain_run(const void* workspace, int n_phases, int64_
     if (!workspace || n_phases < 1 || max_IC <= 0 || max_IC % 128 != 0) { set_error("gemv_w2_chain_run: bad arguments"); return BDQ_ERR_SHAPE; }
     const int nwin = (int)((max_IC / 128 + 3) / 4);
     const int wpw = (nwin + chain::kWarps - 1) / chain::kWarps;
-    const int smem = chain::smem_bytes(wpw);
-    if (smem > 112 * 1024) { set_error("gemv_w2_chain_run: IC too large for two CTAs per SM"); return BDQ_ERR_UNSUPPORTED; }
+    const int smem = chain::smem_bytes(wpw, n_phases);
+    if (smem > 112 * 1024) {
+        set_error("gemv_w2_chain_run: %d phases at max IC %lld need %d B of shared memory (> 112 KB, two CTAs per SM): split the chain",
+                  n_phases, (long long)max_IC, smem);
+        return BDQ_ERR_UNSUPPORTED;
+    }
     const void* kern = reinterpret_cast<const void*>(chain::gemv_w2_chain_kernel);
     if (!ensure_dyn_smem(kern, 112 * 1024)) return check_launch("bdq_gemv_w2_chain(attr)");
     int occ = 0;
@@ -482,7 +544,6 @@ extern "C" int bdq_gemv_w2_chain_run(const void* workspace, int n_phases, int64_
     const size_t plan_bytes = (size_t)n_phases * sizeof(chain::Phase);
     const chain::Phase* plan = (const chain::Phase*)workspace;
     unsigned int* counters = (unsigned int*)((const uint8_t*)workspace + ((plan_bytes + 255) & ~(size_t)255));
-    if (lookahead < 1) lookahead = 2;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(sm_count() * 2));
     cfg.blockDim = dim3(chain::kThreads);
@@ -493,6 +554,9 @@ extern "C" int bdq_gemv_w2_chain_run(const void* workspace, int n_phases, int64_
     at[0].val.cooperative = 1;
     cfg.attrs = at;
     cfg.numAttrs = 1;
-    cudaLaunchKernelEx(&cfg, chain::gemv_w2_chain_kernel, plan, n_phases, wpw, counters, lookahead);
+    static int dbg = -1;   // BDQ_CHAIN_DEBUG (dev experiments only): 1 = skip the barrier waits (wrong results), 2 = no L2 prefetch
+    if (dbg < 0) { const char* e = getenv("BDQ_CHAIN_DEBUG"); dbg = e ? atoi(e) : 0; }
+    unsigned long long* prof = (g_chain_prof && g_chain_prof_cap >= (int64_t)sm_count() * 2 * n_phases * 8) ? g_chain_prof : nullptr;
+    cudaLaunchKernelEx(&cfg, chain::gemv_w2_chain_kernel, plan, n_phases, wpw, counters, lookahead, prof, dbg);
     return check_launch("bdq_gemv_w2_chain_run");
 }

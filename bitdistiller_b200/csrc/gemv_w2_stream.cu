@@ -23,9 +23,9 @@
 //     one LOP3 per four codes, no shift; digit i accumulates in its own int32 tile and the 4^-i factors are applied in
 //     the fp32 fix-up (all intermediate values are integers below 2^24, i.e. exact).  An fp16 mma.sync formulation
 //     ((word & mask) | exponent, 9 ALU ops per 16 codes) was measured first and was ALU-pipe bound at ~0.7x the HBM rate;
-//   * x becomes block fixed point per quantisation group while it is staged: q = rint(x / unit) with |q| <= 8192 and
-//     unit a power of two from the group's largest magnitude, split into two int8 limbs q = 256 hi + lo (error
-//     <= 2^-14 of the group maximum per element, below the fp16 rounding of x itself for the elements that matter);
+//   * x becomes block fixed point per quantisation group while it is staged: q = rint(x / unit) with |q| <= 32512 and
+//     unit = (the group's largest magnitude) / 32512, split into two int8 limbs q = 256 hi + lo (error <= 2^-16 of the
+//     group maximum per element, below the fp16 rounding of x itself for the elements that matter);
 //   * with batch 1 the N dimension of the MMA keeps the four quantisation groups of a 512-wide K window AND the two
 //     limbs apart: lane t of a quad holds group t, B column 2*group + limb carries that limb of x for the k rows of
 //     group `group` only (zero elsewhere), so every lane ends up with the (hi, lo) sums of its own group and the
@@ -328,7 +328,7 @@ __global__ void __launch_bounds__(kSThreads, 2) gemv_w2s_kernel(const __half* __
     mark();   // 1: weight loads issued
     if constexpr (PDL) asm volatile("griddepcontrol.wait;" ::: "memory");
     mark();   // 2: dependency resolved
-    // Each group of 128 activations becomes block fixed point: q = rint(x / unit), |q| <= 8192, unit a power of two
+    // Each group of 128 activations becomes block fixed point: q = rint(x / unit), |q| <= 32512, unit = group max / 32512;
     // taken from the group's largest magnitude; q = 256 * hi + lo with int8 limbs.  Lane l owns word l of the window
     // (16 activations); byte j of register i of a limb holds activation i + 4j of the word, the order in which
     // (word & (0x03030303 << 2i)) presents the codes.
@@ -356,11 +356,14 @@ __global__ void __launch_bounds__(kSThreads, 2) gemv_w2s_kernel(const __half* __
             mx = max(mx & 0xffffu, mx >> 16);   // |.| bit patterns order like unsigned integers, NaN > Inf > finite
 #pragma unroll
             for (int sft = 1; sft < 8; sft <<= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, sft));
-            const uint32_t ex = (mx >> 10) & 31u;              // fp16 exponent field: |x| < 2^(max(ex,1) - 14)
-            const uint32_t exc = ex < 1u ? 1u : ex;
-            const float inv_unit = __uint_as_float((154u - exc) << 23);                        // 2^(27 - exc)
-            // unit = 2^(exc - 27): |x / unit| < 8192.  A non-finite activation makes the unit (and the outputs) NaN.
-            const float unit = ex == 31u ? __uint_as_float(0x7fc00000u) : __uint_as_float((exc + 100u) << 23);
+            const uint32_t ex = (mx >> 10) & 31u;              // fp16 exponent field (31: Inf / NaN)
+            // unit = max|x| / 32512 (127 * 256): the largest element becomes q = 32512, i.e. hi = 127, lo = 0 -- both limbs use
+            // their full int8 range (a power-of-two unit left 2-3 bits unused: with a 1000x outlier channel in the group the
+            // other 127 activations kept ~4 bits and rows with small weights on the outlier missed rtol 1e-2).
+            // A non-finite activation makes the unit (and the outputs) NaN; an all-zero group gets the smallest fp16 step.
+            const float gm = fmaxf(__half2float(__ushort_as_half((unsigned short)mx)), 5.9604645e-8f);
+            const float inv_unit = __fdividef(32512.f, gm);
+            const float unit = ex == 31u ? __uint_as_float(0x7fc00000u) : gm * (1.f / 32512.f);
             // q = rint(x / unit) by the 1.5 * 2^23 trick with 128 folded in: bits = 0x4B400080 + q.  With
             // q = 256 hi + lo, lo in [-128, 127]:  hi = byte 1 of bits, lo = byte 0 of bits ^ 0x80 (both as int8).
             uint32_t bits[16], qsum = 0;
@@ -476,8 +479,9 @@ __global__ void __launch_bounds__(kSThreads, 2) gemv_w2s_kernel(const __half* __
             imma16832(acc[3], a0 & 0xC0C0C0C0u, a1 & 0xC0C0C0C0u, a2 & 0xC0C0C0C0u, a3 & 0xC0C0C0C0u, q1.z, q1.w);
         }
         // this lane's columns 2t, 2t+1 = (hi, lo) limb sums of group t: rows g (acc[.][0..1]) and g+8 (acc[.][2..3]).
-        // Plane i carries 4^i: u = 64 a0 + 16 a1 + 4 a2 + a3 = 64 * sum code * limb (|u| < 2^24), then
-        // 256 u_hi + u_lo - z * 64 sum q = 64 * sum (code - z) * q  (< 2^28: int32 exact, one rounding in the I2F).
+        // Plane i carries 4^i: u = 64 a0 + 16 a1 + 4 a2 + a3 = 64 * sum code * limb (|u| <= 64 * 128 * 3 * 128 < 2^22), then
+        // 256 u_hi + u_lo - z * 64 sum q = 64 * sum (code - z) * q  (|.| <= 805e6 + 799e6 < 2^31: int32 exact, one rounding
+        // in the I2F).
         const float2 mt = *reinterpret_cast<const float2*>(wbase + (size_t)c_j * kWinStride + kMetaOff + t * 8);   // (unit/64, 64 sum q)
         const int sq64 = __float_as_int(mt.y);
         const int sh = ((4 * (warp + kSWarps * c_j) + t) & 15) * 2;

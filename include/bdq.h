@@ -152,11 +152,12 @@ int bdq_gemv_w2_multi(const void* x, int nmat, const int32_t* const* qweight, co
  * is an external input that is ready at launch).  This replaces the per-linear gemv_forward_cuda launches of a decoded
  * token (quantization/qmodule.py:166; inference/modules/fused_mlp.py:44-114, fused_attn.py:304-340 ->
  * inference/kernels/csrc/quantization/gemv_cuda.cu:289-346): 2 CTAs per SM stay resident, a grid barrier on an L2 counter
- * replaces the launch boundary between dependent phases, and one lane per CTA prefetches the packed weights of the next
- * `lookahead` phases HBM -> L2 so that HBM keeps streaming while the CTAs wait.
+ * replaces the launch boundary between dependent phases, and the weight loads of the following phases are already in
+ * flight while a phase is reduced, stored and signalled (the weights do not depend on x).
+ *   bdq_gemv_w2_chain_max_phases(max_IC)  phases one run can hold (the plan is kept in shared memory); split longer chains
  *   bdq_gemv_w2_chain_workspace_bytes(n)  device bytes the caller must provide (256-byte aligned)
  *   bdq_gemv_w2_chain_prepare(...)        validates the phases and writes the device-side plan (synchronous, once per model)
- *   bdq_gemv_w2_chain_run(...)            one cooperative launch; max_IC = the largest IC of the plan; lookahead <= 0 -> 2
+ *   bdq_gemv_w2_chain_run(...)            one cooperative launch; max_IC = the largest IC of the plan; `lookahead` is reserved
  * The workspace also holds the barrier counters: two runs of the same workspace must not overlap (one stream).
  */
 #define BDQ_GEMV_CHAIN_NOWAIT 256
@@ -173,10 +174,12 @@ typedef struct bdq_gemv_phase {
     void* out[4];
     int64_t OC[4];
 } bdq_gemv_phase_t;
+int bdq_gemv_w2_chain_max_phases(int64_t max_IC);
 int64_t bdq_gemv_w2_chain_workspace_bytes(int n_phases);
 int bdq_gemv_w2_chain_prepare(const bdq_gemv_phase_t* phases, int n_phases, void* workspace, int64_t workspace_bytes,
                               bdq_stream_t stream);
 int bdq_gemv_w2_chain_run(const void* workspace, int n_phases, int64_t max_IC, int lookahead, bdq_stream_t stream);
+int bdq_gemv_w2_chain_set_prof(void* device_buf_u64, int64_t capacity_u64);   /* dev tool: per-phase %globaltimer marks */
 
 /*
  * Packed NF3 (3 bits per weight + two fp16 scales per group).  The reference has no packed NF3 format or kernel

@@ -341,14 +341,15 @@ def test_decode_chain_equals_launch_sequence(hidden, kv, inter, layers, silu):
     torch.cuda.synchronize()
     ref = [o.clone() for o in outs()]
     assert all(bool(r.isfinite().all()) and float(r.abs().max()) > 0 for r in ref)
-    chain = E.DecodeChain(phases)
-    for rep in range(3):
-        for o in outs():
-            o.zero_()
-        chain.run(lookahead=1 + rep)
-        torch.cuda.synchronize()
-        for i, (a, b) in enumerate(zip(outs(), ref)):
-            assert torch.equal(a, b), (rep, i, float((a.float() - b.float()).abs().max()))
+    for cap in (None, 5):    # 5: the chain split over several launches (a launch holds a bounded number of phases)
+        chain = E.DecodeChain(phases, max_phases_per_launch=cap)
+        for rep in range(3):
+            for o in outs():
+                o.zero_()
+            chain.run()
+            torch.cuda.synchronize()
+            for i, (a, b) in enumerate(zip(outs(), ref)):
+                assert torch.equal(a, b), (cap, rep, i, float((a.float() - b.float()).abs().max()))
 
 
 def test_decode_chain_errors():

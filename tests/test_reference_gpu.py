@@ -97,7 +97,7 @@ def test_ste_quantizers_vs_reference_cuda_autograd(ref, dname):
             rng = wg.amax(1, keepdim=True) - wg.amin(1, keepdim=True)
             agree = ((yr.detach().double().cpu().reshape(-1, G) - y64.detach().cpu().reshape(-1, G)).abs()
                      <= 0.04 * rng + 1e-12).all(1)
-            noise64 = {torch.float32: 1e-7, torch.bfloat16: 2e-2, torch.float16: 2e-2}[dt]
+            noise64 = {torch.float32: 1e-7, torch.bfloat16: 4e-2, torch.float16: 1e-2}[dt]
             bad = ((gw - g64).abs() > 2.01 * ulp_of(g64, dt) + noise64 * gs + 1e-30)[agree]
             assert not bool(bad.any()), (dname, name, G, wi, "vs f64 autograd", int(bad.sum()))
             agree_tot, tot, n = agree_tot + int(agree.sum()), tot + agree.numel(), n + 1

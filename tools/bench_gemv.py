@@ -161,8 +161,7 @@ def main():
                     key = f"{vname:14s} {'fused(4/layer)' if fused else 'split(7/layer)'} {pname:9s} {'+L2hint' if pre else ''}"
                     res[key] = graph_time(ops, vf | pf, fused, dev, pre)
     if batch == 1:
-        for la in (1, 2, 3, 4, 6):
-            res[f"persistent chain (1 launch/token) lookahead {la}"] = chain_time(ops, la)
+        res["persistent chain (1 launch/token)"] = chain_time(ops, 0)
     for k, t in res.items():
         print(f"batch {batch} {k:50s}: {t*1e6:8.1f} us/token  {1/t:8.1f} tok/s  {nbytes/t/1e9:7.1f} GB/s  "
               f"{nbytes/t/1e9/peak*100:5.1f}% of measured HBM peak ({nbytes/1e9:.3f} GB/token)")
