@@ -375,6 +375,11 @@ static int launch_autoclip(const AcArgs& a, cudaStream_t st) {
     return check_launch("bdq_autoclip");
 }
 
+// autoclip_tc.cu: tcgen05 + TMA kernel for 16-bit dtypes, group 128, <= 512 tokens
+int launch_autoclip_tc(const void* w, const void* x, void* best_max, void* best_min, int32_t* best_idx, float* best_err, int64_t co,
+                       int64_t ci, int64_t n_tok, int64_t xs, int group, int bits, int quant_type, int n_grid, int nc, int dtype, int sem,
+                       cudaStream_t st);
+
 }  // namespace bdq
 
 using namespace bdq;
@@ -396,6 +401,11 @@ extern "C" int bdq_autoclip(const void* w, const void* x, void* best_max, void* 
     if (co == 0) return BDQ_OK;
     if (!w || !x || !best_max || !best_min) { set_error("null tensor pointer"); return BDQ_ERR_SHAPE; }
     if (ci / group > 65535 * 32 || (co + kAcOT - 1) / kAcOT > 65535) { set_error("autoclip: shape too large"); return BDQ_ERR_SHAPE; }
+    {   // Blackwell-native path first (tcgen05 MMA, TMA-staged X); BDQ_ERR_UNSUPPORTED = not its shape
+        const int rc = launch_autoclip_tc(w, x, best_max, best_min, best_idx, best_err, co, ci, n_tok, x_row_stride, group, bits,
+                                          quant_type, n_grid, nc, dtype, sem, (cudaStream_t)stream);
+        if (rc != BDQ_ERR_UNSUPPORTED) return rc;
+    }
     AcArgs a;
     a.w = w; a.x = x; a.best_max = best_max; a.best_min = best_min; a.best_idx = best_idx; a.best_err = best_err;
     a.co = co; a.ci = ci; a.n_tok = n_tok; a.xs = x_row_stride;

@@ -125,7 +125,9 @@ __global__ void __launch_bounds__(kGmThreads, 1) gemm_w2_kernel(const __grid_con
                                                                 const GemmPeers peers) {
     constexpr int kGmStages = GmCfg<MT>::kStages, kGmStageBytes = GmCfg<MT>::kStageBytes;
     extern __shared__ uint8_t gm_smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(gm_smem_raw) + 1023) & ~(uintptr_t)1023);
+    // align on the 32-bit shared address and ADD the offset, so that the pointer keeps its shared address space (STS / LDS
+    // instead of generic ST / LD: the round trip through uintptr_t made all 280 stores of this kernel generic ones)
+    uint8_t* smem = gm_smem_raw + ((1024u - (gm_smem_u32(gm_smem_raw) & 1023u)) & 1023u);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kGmStages * kGmStageBytes);
     uint64_t* full_a = bars;                    // [stages] TMA landed
     uint64_t* full_b = bars + kGmStages;        // [stages] dequant written (256 arrivals)
