@@ -44,12 +44,14 @@ struct Smem {   // offsets from the 1024-aligned base
     static constexpr int x = 0;
     static constexpr int a = x + kXBytes;                       // 2 buffers
     static constexpr int cand = a + 2 * kABytes;                // [2][kRowsUsed][12] floats
-    static constexpr int wfp = cand + 2 * kRowsUsed * kCandFloats * 4;   // [2][64] packed T pairs (the raw weight group)
+    static constexpr int candp = cand + 2 * kRowsUsed * kCandFloats * 4;  // [2][kRowsUsed][8] u32: T pairs lo, hi, T1, T2, T3, -z, s + mode
+    static constexpr int wfp = candp + 2 * kRowsUsed * 8 * 4;           // [2][64] packed T pairs (the raw weight group)
     static constexpr int ext = wfp + 2 * 256;                   // [kOT][2] floats: group max / min per channel
     static constexpr int errh = ext + kOT * 8;                  // [2 parity][2 halves][128] floats
     static constexpr int owb = errh + 2 * 2 * 128 * 4;          // [kNEpiWarps][2][32] floats
     static constexpr int wred = owb + kNEpiWarps * 256;         // [kNParamWarps][2] floats
-    static constexpr int bars = wred + 64;                      // mbarriers
+    static constexpr int fac = wred + 64;                       // [16] floats: (float)(1 - i / n_grid), the python-double shrink factors
+    static constexpr int bars = fac + 64;                       // mbarriers
     static constexpr int tmem_slot = bars + 16 * 8;
     static constexpr int total = tmem_slot + 16 + 1024;         // + alignment slack
 };
@@ -64,6 +66,7 @@ struct Args {
     float* best_err;
     int64_t co, ci, n_tok;
     int bits, quant_type, n_grid, nc, sem;
+    long long* prof;   // dev tool (BDQ_AUTOCLIP_TC_PROF): cycles every role of CTA (0, 0) spent waiting, see tools/prof_autoclip_roles.py
     Nf3Tables tb;
 };
 
@@ -81,10 +84,10 @@ __device__ __forceinline__ void mbar_wait(uint64_t* b, uint32_t parity) {
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
         "AW_%=:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t"
         "@p bra AD_%=;\n\t"
         "bra AW_%=;\n\t"
-        "AD_%=:\n\t}" ::"r"(s_u32(b)), "r"(parity) : "memory");
+        "AD_%=:\n\t}" ::"r"(s_u32(b)), "r"(parity), "r"(0x989680u) : "memory");   // suspend-time hint: the warp sleeps, it does not spin
 }
 // K-major SWIZZLE_128B shared-memory matrix descriptor (see gemm_w2.cu:gm_desc)
 __device__ __forceinline__ uint64_t sdesc(uint32_t smem_addr) {
@@ -123,11 +126,13 @@ __global__ void __launch_bounds__(kThreads, 1) autoclip_tc_kernel(const __grid_c
     uint8_t* Xs = smem + Smem::x;
     uint8_t* As = smem + Smem::a;
     float* cand = reinterpret_cast<float*>(smem + Smem::cand);
+    uint32_t* candp = reinterpret_cast<uint32_t*>(smem + Smem::candp);
     uint32_t* wfp = reinterpret_cast<uint32_t*>(smem + Smem::wfp);
     float* ext = reinterpret_cast<float*>(smem + Smem::ext);
     float* errh = reinterpret_cast<float*>(smem + Smem::errh);
     float* owb = reinterpret_cast<float*>(smem + Smem::owb);
     float* wred = reinterpret_cast<float*>(smem + Smem::wred);
+    float* facs = reinterpret_cast<float*>(smem + Smem::fac);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Smem::bars);
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + Smem::tmem_slot);
 
@@ -153,6 +158,7 @@ __global__ void __launch_bounds__(kThreads, 1) autoclip_tc_kernel(const __grid_c
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&xmap) : "memory");
     }
+    if (tid < 16) facs[tid] = (float)(1.0 - (double)tid / (double)a.n_grid);   // org * (1 - i / n_grid): python double, cast to fp32 opmath
     for (int i = tid; i < 2 * kABytes / 16; i += kThreads) reinterpret_cast<uint4*>(As)[i] = make_uint4(0, 0, 0, 0);
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     if (warp == kWarpMma) {
@@ -163,6 +169,18 @@ __global__ void __launch_bounds__(kThreads, 1) autoclip_tc_kernel(const __grid_c
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_d = *tmem_slot;
+    // dev tool: per-role wait accounting of CTA (0, 0), lane 0 of each warp: prof[warp * 8 + slot] += cycles waited
+    const bool profiling = a.prof != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && lane == 0;
+    long long t_role0 = profiling ? clock64() : 0;
+    auto wait_t = [&](uint64_t* b, uint32_t parity, int slot) {
+        if (profiling) {
+            const long long t0 = clock64();
+            mbar_wait(b, parity);
+            a.prof[warp * 8 + slot] += clock64() - t0;
+        } else {
+            mbar_wait(b, parity);
+        }
+    };
 
     if (warp == kWarpMma) {
         // =========================== TMA (X once) + MMA issue ===========================
@@ -175,12 +193,12 @@ __global__ void __launch_bounds__(kThreads, 1) autoclip_tc_kernel(const __grid_c
             const uint32_t xa = s_u32(Xs), aa = s_u32(As);
             for (int ol = 0; ol < no; ++ol) {
                 const int ab = ol & 1;
-                mbar_wait(&bars[kBarAFull + ab], (uint32_t)((ol >> 1) & 1));
+                wait_t(&bars[kBarAFull + ab], (uint32_t)((ol >> 1) & 1), 0);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
                     if (ol > 0) {
-                        mbar_wait(&bars[kBarAccEmpty + h], (uint32_t)((ol - 1) & 1));
+                        wait_t(&bars[kBarAccEmpty + h], (uint32_t)((ol - 1) & 1), 1 + h);
                         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                     }
 #pragma unroll
@@ -205,7 +223,7 @@ __global__ void __launch_bounds__(kThreads, 1) autoclip_tc_kernel(const __grid_c
             const float v = vnext;
             if (ol + 1 < no) vnext = load_scalar<DT>(a.w, (o0 + ol + 1) * a.ci + (int64_t)g * kG + pt);   // hide the global latency
             const float mxw = group_max<32>(v), mnw = group_min<32>(v);
-            if (ol >= 2) mbar_wait(&bars[kBarPEmpty + pb], (uint32_t)(((ol >> 1) - 1) & 1));   // the row warps are done with this buffer
+            if (ol >= 2) wait_t(&bars[kBarPEmpty + pb], (uint32_t)(((ol >> 1) - 1) & 1), 0);   // the row warps are done with this buffer
             if (lane == 0) { wred[(warp - kWarpParam0) * 2] = mxw; wred[(warp - kWarpParam0) * 2 + 1] = mnw; }
             // raw T pairs of the group for the row generators
             const float vn = __shfl_down_sync(0xffffffffu, v, 1);
@@ -230,8 +248,8 @@ __global__ void __launch_bounds__(kThreads, 1) autoclip_tc_kernel(const __grid_c
                 } else {
                     const int ip = c / nc, in = c - ip * nc;
                     // org * (1 - i / n_grid): python double factor, cast to fp32 opmath, product rounded to T (autoclip.py:50,52)
-                    const float hi = rT<DT>(mx * (float)(1.0 - (double)ip / (double)a.n_grid));
-                    const float lo = rT<DT>(mn * (float)(1.0 - (double)in / (double)a.n_grid));
+                    const float hi = rT<DT>(mx * facs[ip]);
+                    const float lo = rT<DT>(mn * facs[in]);
                     const float cmx = fminf(fmaxf(mx, lo), hi), cmn = fminf(fmaxf(mn, lo), hi);   // extremes of clamp(w, lo, hi)
                     cp[4] = lo; cp[5] = hi; cp[7] = 0.f;
                     if (a.quant_type == BDQ_QUANT_INT) {
@@ -253,6 +271,15 @@ __global__ void __launch_bounds__(kThreads, 1) autoclip_tc_kernel(const __grid_c
                     }
                 }
             }
+            if (pt < kRowsUsed) {   // the same parameters as duplicated T pairs + a mode word: the row generators read two LDS.128
+                using P = P2<DT>;
+                const float* cp = cand + (pb * kRowsUsed + pt) * kCandFloats;
+                // mode: 0 threshold form, 1 pass-through (weight row), 2 unused slot, 3 op by op
+                const uint32_t mode = cp[7] == 1.f ? 1u : (cp[7] == 2.f ? 2u : (cp[11] != 0.f ? 0u : 3u));
+                uint4* dp = reinterpret_cast<uint4*>(candp + (pb * kRowsUsed + pt) * 8);
+                dp[0] = make_uint4(P::bits(P::dup(cp[4])), P::bits(P::dup(cp[5])), P::bits(P::dup(cp[8])), P::bits(P::dup(cp[9])));
+                dp[1] = make_uint4(P::bits(P::dup(cp[10])), P::bits(P::dup(-cp[2])), P::bits(P::dup(cp[0])), mode);
+            }
             mbar_arrive(&bars[kBarPFull + pb]);
             bar_sync(1, kNParamWarps * 32);   // wred is rewritten by the next channel
         }
@@ -265,29 +292,32 @@ __global__ void __launch_bounds__(kThreads, 1) autoclip_tc_kernel(const __grid_c
         using h2 = typename P::h2;
         for (int ol = 0; ol < no; ++ol) {
             const int pb = ol & 1, ab = ol & 1;
-            mbar_wait(&bars[kBarPFull + pb], (uint32_t)((ol >> 1) & 1));
-            if (ol >= 2) mbar_wait(&bars[kBarAEmpty + ab], (uint32_t)(((ol >> 1) - 1) & 1));   // the MMAs that read this buffer retired
+            wait_t(&bars[kBarPFull + pb], (uint32_t)((ol >> 1) & 1), 0);
+            if (ol >= 2) wait_t(&bars[kBarAEmpty + ab], (uint32_t)(((ol >> 1) - 1) & 1), 1);   // the MMAs that read this buffer retired
             const uint4 wraw = *reinterpret_cast<const uint4*>(wfp + pb * 64 + jt * 4);         // this thread's 8 weights (4 T pairs)
             const uint32_t wp[4] = {wraw.x, wraw.y, wraw.z, wraw.w};
             uint8_t* abase = As + ab * kABytes + kh * (kABytes / 2);
             for (int slot = rt >> 4; slot < kRowsUsed; slot += (kNRowWarps * 32) / 16) {
-                const float* cp = cand + (pb * kRowsUsed + slot) * kCandFloats;
-                if (cp[7] == 2.f) continue;
+                const uint4 pa = *reinterpret_cast<const uint4*>(candp + (pb * kRowsUsed + slot) * 8);
+                const uint4 pq = *reinterpret_cast<const uint4*>(candp + (pb * kRowsUsed + slot) * 8 + 4);
+                const uint32_t mode = pq.w;
+                if (mode == 2u) continue;
                 const int row = row_of_slot(slot);
                 uint32_t o4[4];
-                if (cp[7] == 1.f) {
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) o4[i] = wp[i];
-                } else if (cp[11] != 0.f) {   // threshold form: clamp, count the thresholds passed, (count - z) * s
-                    const h2 lo2 = P::dup(cp[4]), hi2 = P::dup(cp[5]), t1 = P::dup(cp[8]), t2 = P::dup(cp[9]), t3 = P::dup(cp[10]);
-                    const h2 nz2 = P::dup(-cp[2]), s2 = P::dup(cp[0]);
+                if (mode == 0u) {   // threshold form: clamp, count the thresholds passed, (count - z) * s
+                    const h2 lo2 = P::from_bits(pa.x), hi2 = P::from_bits(pa.y), t1 = P::from_bits(pa.z), t2 = P::from_bits(pa.w);
+                    const h2 t3 = P::from_bits(pq.x), nz2 = P::from_bits(pq.y), s2 = P::from_bits(pq.z);
 #pragma unroll
                     for (int i = 0; i < 4; ++i) {
                         const h2 x2 = __hmin2(__hmax2(P::from_bits(wp[i]), lo2), hi2);
                         const h2 c2 = __hadd2(__hadd2(__hge2(x2, t1), __hge2(x2, t2)), __hge2(x2, t3));
                         o4[i] = P::bits(__hmul2(__hadd2(c2, nz2), s2));   // rT((c - z) * s)
                     }
+                } else if (mode == 1u) {
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) o4[i] = wp[i];
                 } else {
+                    const float* cp = cand + (pb * kRowsUsed + slot) * kCandFloats;
 #pragma unroll
                     for (int i = 0; i < 4; ++i) {
                         float v[2] = {P::lo(P::from_bits(wp[i])), P::hi(P::from_bits(wp[i]))};
@@ -323,7 +353,7 @@ __global__ void __launch_bounds__(kThreads, 1) autoclip_tc_kernel(const __grid_c
         float* myow = owb + ew * 64;
         const float inv_tok = 1.0f / (float)a.n_tok;
         for (int ol = 0; ol < no; ++ol) {
-            mbar_wait(&bars[kBarAccFull + half], (uint32_t)(ol & 1));
+            wait_t(&bars[kBarAccFull + half], (uint32_t)(ol & 1), 0);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             float e0 = 0.f, e1 = 0.f, e2 = 0.f, e3 = 0.f;
             // 16 chunks of 16 tokens, software-pipelined: the TMEM load of chunk cb + 1 is in flight while chunk cb is reduced
@@ -391,8 +421,8 @@ __global__ void __launch_bounds__(kThreads, 1) autoclip_tc_kernel(const __grid_c
                     float bmax = mx, bmin = mn;
                     if (bi >= 0) {
                         const int ip = bi / nc, in = bi - ip * nc;
-                        bmax = rT<DT>(mx * (float)(1.0 - (double)ip / (double)a.n_grid));
-                        bmin = rT<DT>(mn * (float)(1.0 - (double)in / (double)a.n_grid));
+                        bmax = rT<DT>(mx * facs[ip]);
+                        bmin = rT<DT>(mn * facs[in]);
                     }
                     store_scalar<DT>(a.best_max, o * ng + g, bmax);
                     store_scalar<DT>(a.best_min, o * ng + g, bmin);
@@ -403,6 +433,7 @@ __global__ void __launch_bounds__(kThreads, 1) autoclip_tc_kernel(const __grid_c
             (void)et;
         }
     }
+    if (profiling) a.prof[warp * 8 + 7] = clock64() - t_role0;   // lifetime of the role
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     if (warp == kWarpMma) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(512) : "memory");
@@ -425,6 +456,7 @@ static EncodeTiledFn get_encode() {
 
 }  // namespace actc
 
+static long long* g_actc_prof = nullptr;
 // Returns BDQ_ERR_UNSUPPORTED when the shape is not this kernel's (the caller then runs autoclip.cu's kernel).
 int launch_autoclip_tc(const void* w, const void* x, void* best_max, void* best_min, int32_t* best_idx, float* best_err, int64_t co,
                        int64_t ci, int64_t n_tok, int64_t xs, int group, int bits, int quant_type, int n_grid, int nc, int dtype, int sem,
@@ -453,6 +485,7 @@ int launch_autoclip_tc(const void* w, const void* x, void* best_max, void* best_
     a.co = co; a.ci = ci; a.n_tok = n_tok;
     a.bits = bits; a.quant_type = quant_type; a.n_grid = n_grid; a.nc = nc; a.sem = sem;
     a.tb = make_tables(dtype, sem);
+    a.prof = g_actc_prof;
     dim3 grid((unsigned)(ci / kG), (unsigned)((co + kOT - 1) / kOT));
     if (dtype == BDQ_BF16) {
         if (!ensure_dyn_smem(reinterpret_cast<const void*>(autoclip_tc_kernel<kBF16>), Smem::total)) return check_launch("bdq_autoclip(tc attr)");
@@ -465,3 +498,9 @@ int launch_autoclip_tc(const void* w, const void* x, void* best_max, void* best_
 }
 
 }  // namespace bdq
+
+// dev tool: device buffer of 32 x 8 int64 (zeroed by the caller) that later tcgen05 autoclip launches accumulate wait cycles into
+extern "C" int bdq_autoclip_tc_set_prof(void* buf) {
+    bdq::g_actc_prof = (long long*)buf;
+    return BDQ_OK;
+}

@@ -47,10 +47,10 @@ __device__ __forceinline__ void gm_mbar_wait(uint64_t* b, uint32_t parity) {
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
         "GW_%=:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t"
         "@p bra GD_%=;\n\t"
         "bra GW_%=;\n\t"
-        "GD_%=:\n\t}" ::"r"(gm_smem_u32(b)), "r"(parity) : "memory");
+        "GD_%=:\n\t}" ::"r"(gm_smem_u32(b)), "r"(parity), "r"(0x989680u) : "memory");   // suspend-time hint: the warp sleeps, it does not spin
 }
 
 // K-major, SWIZZLE_128B shared-memory matrix descriptor (cute::UMMA::SmemDescriptor layout): start address >> 4 in

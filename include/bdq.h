@@ -293,6 +293,7 @@ int bdq_int2_shard_encode_multi(int nseg, const void* const* w, const int64_t* n
 int bdq_autoclip(const void* w, const void* x, void* best_max, void* best_min, int32_t* best_idx, float* best_err,
                  int64_t co, int64_t ci, int64_t n_tok, int64_t x_row_stride, int group, int bits, int quant_type,
                  int n_grid, double max_shrink, int dtype, int sem, bdq_stream_t stream);
+int bdq_autoclip_tc_set_prof(void* device_buf_256_int64);   /* dev tool: per-role wait cycles of the tcgen05 kernel, CTA (0, 0) */
 
 #ifdef __cplusplus
 }

@@ -23,7 +23,7 @@ for name, co, ci in [("v/o_proj", 4096, 4096), ("gate/up_proj", 11008, 4096), ("
     t = e0.elapsed_time(e1) * 1e-3
     pairs = co * ci // 128
     flop = pairs * 2.0 * 512 * 128 * 101
-    print(f"{qt} {name:14s} [{co}x{ci}] {t*1e3:9.2f} ms  {pairs/t/1e6:7.2f} M pairs/s  {flop/t/1e12:7.1f} TFLOP/s executed (mma.sync)")
+    print(f"{qt} {name:14s} [{co}x{ci}] {t*1e3:9.2f} ms  {pairs/t/1e6:7.2f} M pairs/s  {flop/t/1e12:7.1f} TFLOP/s executed (tcgen05 for 16-bit g128, else mma.sync)")
     mult = {"v/o_proj": 2, "gate/up_proj": 2, "down_proj": 1}[name]
     tot_pairs += pairs * mult
     tot_t += t * mult
