@@ -10,9 +10,10 @@ N > 1: the model is SHARDED the way the reference trains it under ZeRO-3 / FSDP2
     forward : every rank quantises its shard ONCE, the encode kernel stores the 0.28 B/weight int2 payload into every
               rank's symmetric-memory buffer over NVLink (no collective), one barrier, one decode launch rebuilds the
               fake-quantised FULL weights on every rank (what QLinear.forward needs, qlinear.py:75) -- ShardGatherGroup;
-    backward: NCCL reduce-scatter of the gradient w.r.t. the quantised weight (every rank has its own batch's gradient),
-              then ONE fused STE backward launch on the rank's shard (the STE backward is linear in the incoming
-              gradient and group-local, so it commutes with the sum over ranks).
+    backward: every rank pushes the rows of its gradient (every rank has its own batch's gradient) into the owning rank's
+              symmetric-memory inbox over NVLink (bdq_rows_push, no collective), one barrier, then the STE backward of the
+              shard sums the N sources on the fly (bdq_int_ste_bwd_nsrc: the STE backward is linear in the incoming gradient
+              and group-local, so it commutes with the sum over ranks; the reduced gradient is never materialised).
   `sharded.reference_order` in the line = the reference's order on the same shards (NCCL all-gather of the bf16 shards,
   full fake-quant and full STE backward on every rank, then the same reduce-scatter), timed the same way.
 
@@ -180,8 +181,8 @@ def workload_config(n):
     else:
         cfg.update({"parallelism": f"fsdp{n}: dim-0 shards of every linear (ZeRO-3 / FSDP2 layout), quantise-before-"
                                    "all-gather forward over NVLink peer stores, reduce-scatter + shard STE backward",
-                    "launches": "per decoder layer: 1 encode (7 shards) + 1 barrier + 1 decode forward; 7 NCCL "
-                                "reduce-scatters + 1 STE backward launch over the rank's flat shard buffer",
+                    "launches": "per decoder layer: 1 encode (7 shards) + 1 barrier + 1 decode forward; 1 gradient push + "
+                                "1 barrier + 7 multi-source STE backward launches",
                     "l2": "every rank reads its 12.95 GB upstream gradient and writes 12.95 GB of fake-quantised "
                           "weights per step, >> 126 MB L2 (no flush needed)"})
     return cfg
@@ -416,14 +417,19 @@ def run_sharded(args, torch, dist, L, dev, rank, world, local):
     Wsh_v = [views(w, False) for w in Wsh]
     Gfull_v = [views(g, True) for g in Gfull]
     grp = S.ShardGatherGroup(shapes, GROUP, torch.bfloat16, dev, symmetric=True)
+    # backward: gradient push over NVLink peer memory + multi-source STE backward (sharded.ShardGradReducer); the NCCL
+    # reduce-scatter + bdq_int_ste_bwd order is timed next to it after the main measurement
+    red = S.ShardGradReducer(shapes, GROUP, torch.bfloat16, dev) if os.environ.get("BDQ_BENCH_NCCL_RS", "0") != "1" else None
     nbuf = 2
     g_sh = [torch.empty(nshard, device=dev, dtype=torch.bfloat16) for _ in range(nbuf)]     # reduce-scattered gradient shards
     g_sh_v = [views(g, False) for g in g_sh]
     out_gw = [torch.empty(nshard, device=dev, dtype=torch.bfloat16) for _ in range(nbuf)]
+    out_gw_v = [views(g, False) for g in out_gw]
     even = all((b - a) * world == o for (a, b), (o, _) in zip(spans, shapes))
     if not even:
         raise SystemExit("bench.py: the Llama-2-7B shapes shard evenly for N in {2, 4, 8}")
     dec_events, phase = [], []
+    nccl_bwd = [False]
 
     def ev():
         e = torch.cuda.Event(enable_timing=True)
@@ -436,14 +442,22 @@ def run_sharded(args, torch, dist, L, dev, rank, world, local):
             grp.forward(Wsh_v[li], record=dec_events if record else None)
         t1 = ev() if record else None
         rs_ev = []
+        fused = red is not None and not nccl_bwd[0]
+        ticket = red.push(Gfull_v[0]) if fused else None                   # NVLink push of layer 0 (the reducer's own stream)
         for li in range(nlayers):
             b = li % nbuf
             r0 = ev() if record else None
-            for t in range(len(shapes)):
-                dist.reduce_scatter_tensor(g_sh_v[b][t], Gfull_v[li][t], op=dist.ReduceOp.SUM)
-            r1 = ev() if record else None
-            rc = lib.bdq_int_ste_bwd(L.ptr(Wsh[li]), L.ptr(g_sh[b]), L.ptr(out_gw[b]), L.i64(nshard), GROUP, BITS, L.BF16, sem, st)
-            L.check(rc, "bdq_int_ste_bwd")
+            if fused:
+                nxt = red.push(Gfull_v[li + 1]) if li + 1 < nlayers else None   # overlaps this layer's HBM-bound STE launches
+                red.finish(ticket, Wsh_v[li], outs=out_gw_v[b])             # 7 multi-source STE launches
+                ticket = nxt
+                r1 = r0
+            else:
+                for t in range(len(shapes)):
+                    dist.reduce_scatter_tensor(g_sh_v[b][t], Gfull_v[li][t], op=dist.ReduceOp.SUM)
+                r1 = ev() if record else None
+                rc = lib.bdq_int_ste_bwd(L.ptr(Wsh[li]), L.ptr(g_sh[b]), L.ptr(out_gw[b]), L.i64(nshard), GROUP, BITS, L.BF16, sem, st)
+                L.check(rc, "bdq_int_ste_bwd")
             if record:
                 rs_ev.append((r0, r1, ev()))
         if record:
@@ -509,7 +523,23 @@ def run_sharded(args, torch, dist, L, dev, rank, world, local):
     ok_gather = bool(torch.equal(dq_ref.view(torch.int16), grp.flat.view(torch.int16)))
     ok_f, msg_f = verify_slabs(torch, L, full_w, None, grp.flat, None, sem)
     b = li % nbuf
-    ok_b, msg_b = verify_slabs(torch, L, Wsh[li], g_sh[b], None, out_gw[b], sem)
+    # reference reduced gradient of this rank's shard: every rank's rows summed in rank order, one bf16 rounding per addition
+    # (what the fused backward computes; for 2 ranks also what NCCL computes)
+    r_me = []
+    for t, ((o, i), (a, bb_)) in enumerate(zip(shapes, spans)):
+        parts = [torch.empty_like(Gfull_v[li][t]) for _ in range(world)]
+        dist.all_gather(parts, Gfull_v[li][t])
+        acc = parts[0][a:bb_].clone()
+        for k in range(1, world):
+            acc = (acc.float() + parts[k][a:bb_].float()).to(torch.bfloat16)
+        r_me.append(acc.reshape(-1))
+        del parts
+    g_ref = torch.cat(r_me)
+    gw_ref = torch.empty_like(g_ref)
+    L.check(lib.bdq_int_ste_bwd(L.ptr(Wsh[li]), L.ptr(g_ref), L.ptr(gw_ref), L.i64(nshard), GROUP, BITS, L.BF16, sem, st), "verify bwd")
+    ok_red = bool(torch.equal(gw_ref.view(torch.int16), out_gw[b].view(torch.int16))) if red is not None else True
+    ok_b, msg_b = verify_slabs(torch, L, Wsh[li], g_ref if red is not None else g_sh[b], None, out_gw[b], sem)
+    ok_b = ok_b and ok_red
     flag = torch.tensor([int(ok_gather and ok_f and ok_b)], device=dev)
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     verified = bool(flag.item())
@@ -557,6 +587,26 @@ def run_sharded(args, torch, dist, L, dev, rank, world, local):
     except Exception as e:  # the headline line must survive
         ref_order = {"error": f"{type(e).__name__}: {e}"[:300]}
 
+    # ---- our forward with the NCCL reduce-scatter + bdq_int_ste_bwd backward (the round-1 order), 2 timed steps
+    nccl_variant = None
+    if red is not None:
+        try:
+            nccl_bwd[0] = True
+            step()
+            barrier()
+            a, bb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for _ in range(2):
+                step()
+            bb.record()
+            barrier()
+            nccl_variant = {"ms_per_step": maxr(a.elapsed_time(bb) * 1e-3) / 2 * 1e3,
+                            "what": "same forward, backward = 7 NCCL reduce_scatter_tensor calls + one bdq_int_ste_bwd per layer"}
+        except Exception as e:
+            nccl_variant = {"error": f"{type(e).__name__}: {e}"[:300]}
+        finally:
+            nccl_bwd[0] = False
+
     # ---- e2e through the public autograd entry with pinned host buffers (shards in, shard results out)
     try:
         e2e = run_e2e_sharded(torch, dist, S, dev, rank, world, nlayers, shapes, spans, min(args.steps, 2))
@@ -566,14 +616,18 @@ def run_sharded(args, torch, dist, L, dev, rank, world, local):
     bytes_w = weights * 2
     sharded = {
         "fwd_ms": fwd_ms, "bwd_ms": bwd_ms, "decode_ms": dec_ms, "encode_plus_barrier_ms": fwd_ms - dec_ms,
-        "reduce_scatter_ms": rs_ms, "ste_bwd_shard_ms": ste_ms,
+        "backward": ("fused: bdq_rows_push (NVLink peer stores into the owners' symmetric-memory inboxes) + 1 barrier + "
+                     "bdq_int_ste_bwd_nsrc per tensor (gradient summed on the fly, never materialised)") if red is not None else
+                    "NCCL reduce_scatter_tensor per tensor + bdq_int_ste_bwd per layer",
+        "reduce_scatter_ms": rs_ms if red is None else None, "ste_bwd_shard_ms": ste_ms if red is None else None,
+        "nccl_reduce_scatter_variant": nccl_variant,
         "nvlink_bytes_per_rank_per_step": {
             "payload_peer_stores_out": payload_pw * weights / world * (world - 1),
             "reduce_scatter_out_min": bytes_w * (world - 1) / world,
             "reference_order_all_gather_in": bytes_w * (world - 1) / world},
-        "limiter": "the NCCL reduce-scatter of the bf16 weight gradients (12.95 GB per rank per step, inherent to data-parallel "
+        "limiter": "NVLink: every rank must ship (N-1)/N of its 12.95 GB bf16 weight gradient per step (inherent to data-parallel "
                    "training and identical in the reference's order); of the forward, the full-weight decode every rank must run "
-                   "(2.28 B/weight, HBM-bound) -- see fwd_ms / reduce_scatter_ms",
+                   "(2.28 B/weight, HBM-bound) -- see fwd_ms / bwd_ms",
         "reference_order": ref_order}
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": step_s * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -598,6 +652,7 @@ def run_e2e_sharded(torch, dist, S, dev, rank, world, nlayers, shapes, spans, st
     hDQ = [torch.empty_like(t).pin_memory() for t in hW]
     hGW = [torch.empty_like(t).pin_memory() for t in hW]
     grp = S.ShardGatherGroup(shapes, GROUP, torch.bfloat16, dev, symmetric=True)
+    grp.enable_fused_backward()
     dW = [torch.empty_like(t, device=dev) for t in hW]
     dG = [torch.empty_like(t, device=dev) for t in hG]
     t_copy = [0.0]

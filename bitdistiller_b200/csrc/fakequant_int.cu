@@ -17,7 +17,7 @@ namespace bdq {
 bool launch_int_thr_fwd(const void* w, void* dq, const void* cmin, const void* cmax, int64_t n, int G, int bits, int dtype,
                         int round_mode, int sem, cudaStream_t st);
 bool launch_int_thr_bwd(const void* w, const void* gy, void* gw, int64_t n, int G, int bits, int dtype, int sem,
-                        cudaStream_t st);
+                        cudaStream_t st, int n_extra, const void* const* extra);
 
 constexpr int kThreads = 256;
 constexpr int kUnroll = 2;  // 32-byte vectors in flight per lane
@@ -427,8 +427,27 @@ extern "C" int bdq_int_ste_bwd(const void* w, const void* gy, void* gw, int64_t 
     if (!w || !gy || !gw) { set_error("null tensor pointer"); return BDQ_ERR_SHAPE; }
     const float qmax = (float)((1 << bits) - 1);
     cudaStream_t st = (cudaStream_t)stream;
-    if (launch_int_thr_bwd(w, gy, gw, n_elem, group, bits, dtype, sem, st)) return check_launch("bdq_int_ste_bwd(thr)");
+    if (launch_int_thr_bwd(w, gy, gw, n_elem, group, bits, dtype, sem, st, 0, nullptr)) return check_launch("bdq_int_ste_bwd(thr)");
     if (dtype == BDQ_F32) return launch_bwd<kF32>(w, gy, gw, n_elem, group, qmax, sem, st);
     if (dtype == BDQ_BF16) return launch_bwd<kBF16>(w, gy, gw, n_elem, group, qmax, sem, st);
     return launch_bwd<kF16>(w, gy, gw, n_elem, group, qmax, sem, st);
+}
+
+// STE backward whose incoming gradient is the sum of `nsrc` tensors (1..8): gy[0] + gy[1] + ... accumulated in that order with
+// one T rounding per addition.  The reduce-scatter of an FSDP2 gradient and the STE backward of the shard in one pass: gy[i]
+// are this rank's rows of its own gradient and the inbox slots the other ranks pushed theirs into (bdq_rows_push).
+extern "C" int bdq_int_ste_bwd_nsrc(const void* w, int nsrc, const void* const* gy, void* gw, int64_t n_elem, int group, int bits,
+                                    int dtype, int sem, bdq_stream_t stream) {
+    int rc = check_common(n_elem, group, bits, dtype);
+    if (rc) return rc;
+    if (nsrc < 1 || nsrc > 8 || !gy) { set_error("int_ste_bwd_nsrc: nsrc=%d must be 1..8", nsrc); return BDQ_ERR_SHAPE; }
+    if (n_elem == 0) return BDQ_OK;
+    if (!w || !gw) { set_error("null tensor pointer"); return BDQ_ERR_SHAPE; }
+    for (int i = 0; i < nsrc; ++i)
+        if (!gy[i]) { set_error("int_ste_bwd_nsrc: source %d is null", i); return BDQ_ERR_SHAPE; }
+    if (nsrc == 1) return bdq_int_ste_bwd(w, gy[0], gw, n_elem, group, bits, dtype, sem, stream);
+    if (launch_int_thr_bwd(w, gy[0], gw, n_elem, group, bits, dtype, sem, (cudaStream_t)stream, nsrc - 1, gy + 1))
+        return check_launch("bdq_int_ste_bwd_nsrc");
+    set_error("int_ste_bwd_nsrc: needs a 16-bit dtype, bits 2 or 3, group 32/64/128 and 32-byte aligned tensors");
+    return BDQ_ERR_UNSUPPORTED;
 }

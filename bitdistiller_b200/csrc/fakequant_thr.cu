@@ -156,9 +156,19 @@ __device__ __noinline__ void int_bwd_slow_phase2(const void* w, const void* gy, 
     }
 }
 
-template <int DT, int G, int NT>
+// MS (multi-source): the incoming gradient is the sum of gy and ex.n further tensors of the same shape -- the other ranks'
+// gradients of this rank's FSDP2 shard, pushed into a symmetric-memory inbox over NVLink (bdq_rows_push) -- accumulated in
+// the given order with one T rounding per addition (HADD2: the correctly rounded sum of two T values, what a ring
+// reduce-scatter in T computes; for two sources it IS the rounded exact sum).  The reduce-scatter and the STE backward are
+// one pass: the reduced gradient is never materialised.
+struct GySrcs {
+    const uint8_t* p[7];
+    int n;
+};
+
+template <int DT, int G, int NT, bool MS>
 __global__ void __launch_bounds__(kThrThreads, 4) int_thr_bwd_kernel(const uint8_t* __restrict__ w, const uint8_t* __restrict__ gy,
-                                                                  uint8_t* __restrict__ gw, int64_t nchunk, int sem) {
+                                                                  uint8_t* gw, int64_t nchunk, int sem, const GySrcs ex) {
     using P = P2<DT>;
     using h2 = typename P::h2;
     constexpr int LPG = G / 32;
@@ -181,6 +191,19 @@ __global__ void __launch_bounds__(kThrThreads, 4) int_thr_bwd_kernel(const uint8
         } else {
 #pragma unroll
             for (int i = 0; i < 8; ++i) rw[0].r[i] = rw[1].r[i] = rg[0].r[i] = rg[1].r[i] = 0;
+        }
+        if constexpr (MS) {
+            if (valid) {
+#pragma unroll 1
+                for (int sidx = 0; sidx < ex.n; ++sidx) {
+                    const U8 a0 = ldg256(ex.p[sidx] + idx * 64), a1 = ldg256(ex.p[sidx] + idx * 64 + 32);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        rg[0].r[i] = P::bits(__hadd2(P::from_bits(rg[0].r[i]), P::from_bits(a0.r[i])));
+                        rg[1].r[i] = P::bits(__hadd2(P::from_bits(rg[1].r[i]), P::from_bits(a1.r[i])));
+                    }
+                }
+            }
         }
         float mx, mn, mx1, mn1;
         vec_minmax16<DT>(rw[0], mx, mn);
@@ -217,8 +240,18 @@ __global__ void __launch_bounds__(kThrThreads, 4) int_thr_bwd_kernel(const uint8
                 }
             cnt = (int)(P::lo(cx2) + P::hi(cx2)) + ((int)(P::lo(cn2) + P::hi(cn2)) << 16);
         }
+        // op-by-op fallback reads the gradient back from memory: with several sources the summed gradient of this lane's 32
+        // elements is parked in its own slot of gw first (read and rewritten by this thread only)
+        const uint8_t* gsl = gy;
+        if constexpr (MS) {
+            gsl = gw;
+            if (!fast && valid) {
+                stg256(gw + idx * 64, rg[0]);
+                stg256(gw + idx * 64 + 32, rg[1]);
+            }
+        }
         if (!fast && valid) {
-            const float2 r = int_bwd_slow_phase1<DT>(w, gy, idx * 32, p, qmax, mx, mn);
+            const float2 r = int_bwd_slow_phase1<DT>(w, gsl, idx * 32, p, qmax, mx, mn);
             Gs = r.x;
             cnt = __float_as_int(r.y);
         }
@@ -251,7 +284,7 @@ __global__ void __launch_bounds__(kThrThreads, 4) int_thr_bwd_kernel(const uint8
                 stg256(gw + idx * 64 + 32, rg[1]);
             }
         } else if (valid) {
-            int_bwd_slow_phase2<DT>(w, gy, gw, idx * 32, p, qmax, mx, mn, gmax, gmin);
+            int_bwd_slow_phase2<DT>(w, gsl, gw, idx * 32, p, qmax, mx, mn, gmax, gmin);
         }
     }
 }
@@ -270,9 +303,15 @@ static void thr_fwd_g(const uint8_t* w, uint8_t* dq, const void* cmin, const voi
 }
 
 template <int DT, int NT>
-static void thr_bwd_g(const uint8_t* w, const uint8_t* gy, uint8_t* gw, int64_t nchunk, int G, int sem, cudaStream_t st) {
+static void thr_bwd_g(const uint8_t* w, const uint8_t* gy, uint8_t* gw, int64_t nchunk, int G, int sem, cudaStream_t st, const GySrcs& ex) {
     const int64_t nb = thr_blocks(nchunk);
-#define BDQ_L(GG) int_thr_bwd_kernel<DT, GG, NT><<<wave_grid(int_thr_bwd_kernel<DT, GG, NT>, kThrThreads, nb, 16), kThrThreads, 0, st>>>(w, gy, gw, nchunk, sem)
+#define BDQ_L(GG)                                                                                                                        \
+    do {                                                                                                                                 \
+        if (ex.n > 0)                                                                                                                    \
+            int_thr_bwd_kernel<DT, GG, NT, true><<<wave_grid(int_thr_bwd_kernel<DT, GG, NT, true>, kThrThreads, nb, 16), kThrThreads, 0, st>>>(w, gy, gw, nchunk, sem, ex); \
+        else                                                                                                                             \
+            int_thr_bwd_kernel<DT, GG, NT, false><<<wave_grid(int_thr_bwd_kernel<DT, GG, NT, false>, kThrThreads, nb, 16), kThrThreads, 0, st>>>(w, gy, gw, nchunk, sem, ex); \
+    } while (0)
     if (G == 128) BDQ_L(128);
     else if (G == 64) BDQ_L(64);
     else BDQ_L(32);
@@ -303,15 +342,23 @@ bool launch_int_thr_fwd(const void* w, void* dq, const void* cmin, const void* c
     return true;
 }
 
+// n_extra further gradient sources (see GySrcs); 0 = the plain backward
 bool launch_int_thr_bwd(const void* w, const void* gy, void* gw, int64_t n, int G, int bits, int dtype, int sem,
-                        cudaStream_t st) {
+                        cudaStream_t st, int n_extra, const void* const* extra) {
     if ((dtype != kBF16 && dtype != kF16) || (bits != 2 && bits != 3) || (G != 32 && G != 64 && G != 128)) return false;
     if (((uintptr_t)w % 32) || ((uintptr_t)gy % 32) || ((uintptr_t)gw % 32) || (n % 32)) return false;
+    if (n_extra < 0 || n_extra > 7) return false;
+    GySrcs ex;
+    ex.n = n_extra;
+    for (int i = 0; i < 7; ++i) {
+        ex.p[i] = i < n_extra ? (const uint8_t*)extra[i] : nullptr;
+        if (i < n_extra && (!extra[i] || ((uintptr_t)extra[i] % 32))) return false;
+    }
     const uint8_t *wp = (const uint8_t*)w, *gp = (const uint8_t*)gy;
     uint8_t* op = (uint8_t*)gw;
     const int64_t nchunk = n / 32;
-    if (dtype == kBF16) { if (bits == 2) thr_bwd_g<kBF16, 3>(wp, gp, op, nchunk, G, sem, st); else thr_bwd_g<kBF16, 7>(wp, gp, op, nchunk, G, sem, st); }
-    else { if (bits == 2) thr_bwd_g<kF16, 3>(wp, gp, op, nchunk, G, sem, st); else thr_bwd_g<kF16, 7>(wp, gp, op, nchunk, G, sem, st); }
+    if (dtype == kBF16) { if (bits == 2) thr_bwd_g<kBF16, 3>(wp, gp, op, nchunk, G, sem, st, ex); else thr_bwd_g<kBF16, 7>(wp, gp, op, nchunk, G, sem, st, ex); }
+    else { if (bits == 2) thr_bwd_g<kF16, 3>(wp, gp, op, nchunk, G, sem, st, ex); else thr_bwd_g<kF16, 7>(wp, gp, op, nchunk, G, sem, st, ex); }
     return true;
 }
 

@@ -316,3 +316,59 @@ extern "C" int bdq_int2_shard_decode(const void* codes, const void* sz, void* dq
     else decode_g<kF16>((const uint8_t*)codes, (const uint8_t*)sz, (uint8_t*)dq, nchunk, group, st);
     return check_launch("bdq_int2_shard_decode");
 }
+
+
+// ---- gradient push (the scatter half of the fused reduce-scatter + STE backward, bdq_int_ste_bwd_nsrc) ----------------------
+// Up to 64 contiguous segments copied in one launch; the destinations are normally peer-mapped (symmetric memory) inbox slots
+// on the other GPUs, so the kernel's stores ARE the NVLink transfer (no collective, no staging copy).  32-byte vectors.
+namespace bdq {
+constexpr int kPushMaxSeg = 64;
+struct PushSegs {
+    const uint8_t* src[kPushMaxSeg];
+    uint8_t* dst[kPushMaxSeg];
+    unsigned int nvec[kPushMaxSeg];   // 32-byte vectors
+};
+__global__ void __launch_bounds__(256) rows_push_kernel(const __grid_constant__ PushSegs sg) {
+    const int seg = blockIdx.y;
+    const uint8_t* __restrict__ src = sg.src[seg];
+    uint8_t* __restrict__ dst = sg.dst[seg];
+    const unsigned int n = sg.nvec[seg];
+    for (unsigned int i = blockIdx.x * 256u + threadIdx.x; i < n; i += gridDim.x * 256u) stg256(dst + (size_t)i * 32, ldg256(src + (size_t)i * 32));
+}
+}  // namespace bdq
+
+extern "C" int bdq_rows_push(int nseg, const void* const* src, void* const* dst, const int64_t* nbytes, bdq_stream_t stream) {
+    using namespace bdq;
+    if (nseg < 0 || (nseg > 0 && (!src || !dst || !nbytes))) { set_error("rows_push: bad arguments"); return BDQ_ERR_SHAPE; }
+    cudaStream_t st = (cudaStream_t)stream;
+    for (int s0 = 0; s0 < nseg; s0 += kPushMaxSeg) {
+        const int n = nseg - s0 < kPushMaxSeg ? nseg - s0 : kPushMaxSeg;
+        PushSegs sg;
+        memset(&sg, 0, sizeof(sg));
+        int64_t maxvec = 0;
+        for (int i = 0; i < n; ++i) {
+            const int64_t nb = nbytes[s0 + i];
+            if (nb < 0 || nb % 32 != 0 || nb / 32 > 0xffffffffll || !src[s0 + i] || !dst[s0 + i] || ((uintptr_t)src[s0 + i] % 32) ||
+                ((uintptr_t)dst[s0 + i] % 32)) {
+                set_error("rows_push: segment %d must be non-null, 32-byte aligned and a multiple of 32 bytes", s0 + i);
+                return BDQ_ERR_ALIGN;
+            }
+            sg.src[i] = (const uint8_t*)src[s0 + i];
+            sg.dst[i] = (uint8_t*)dst[s0 + i];
+            sg.nvec[i] = (unsigned int)(nb / 32);
+            if (nb / 32 > maxvec) maxvec = nb / 32;
+        }
+        if (maxvec == 0) continue;
+        int64_t bx = (maxvec + 255) / 256;
+        // CTAs per SM in total: 2 x 256 threads already reach the NVLink rate (671 vs 698 GB/s at 8, tools/bench_push.py on 2 x B200)
+        // and leave the SMs to the HBM-bound kernel this transfer is meant to overlap with (BDQ_PUSH_CTAS_PER_SM overrides)
+        int per_sm = 2;
+        { const char* e = getenv("BDQ_PUSH_CTAS_PER_SM"); if (e && atoi(e) > 0) per_sm = atoi(e); }
+        const int64_t cap = (int64_t)sm_count() * per_sm / n + 1;
+        if (bx > cap) bx = cap;
+        rows_push_kernel<<<dim3((unsigned)bx, (unsigned)n), 256, 0, st>>>(sg);
+        const int rc = check_launch("bdq_rows_push");
+        if (rc) return rc;
+    }
+    return BDQ_OK;
+}

@@ -477,11 +477,20 @@ class ShardGatherGroup:
         return self.views
 
 
+    def enable_fused_backward(self):
+        """Use ShardGradReducer (gradient push over NVLink peer memory + multi-source STE backward, no collective, the reduced
+        gradient never materialised) for `backward` instead of NCCL reduce-scatter + bdq_int_ste_bwd."""
+        if self.symmetric and getattr(self, "reducer", None) is None:
+            self.reducer = ShardGradReducer(self.shapes, self.group_size, self.dtype, self.device, self.pg)
+        return getattr(self, "reducer", None) is not None
+
     @torch.no_grad()
     def backward(self, shards, g_fulls, average=False):
         """Per tensor: reduce-scatter of the gradient w.r.t. the quantised weight, then the fused STE backward on the shard
-        (see ShardGather.backward)."""
+        (see ShardGather.backward); with enable_fused_backward() the two are one pass (ShardGradReducer)."""
         from . import _lib as L
+        if getattr(self, "reducer", None) is not None and not average and all(g is not None for g in g_fulls):
+            return self.reducer.backward(list(shards), [g.to(self.dtype) for g in g_fulls])
         out = []
         for t, (w_shard, g_full) in enumerate(zip(shards, g_fulls)):
             if g_full is None:
@@ -533,3 +542,127 @@ class _ShardGatherFn(torch.autograd.Function):
 def quantized_all_gather(w_shard, gatherer, average=False):
     """Autograd entry: shard parameter -> fake-quantised full weight (see ShardGather)."""
     return _ShardGatherFn.apply(w_shard, gatherer, average)
+
+
+# ------------------------------------------------------------------------------------------------- gradient push + fused STE
+class ShardGradReducer:
+    """The backward half of the sharded QAT step as ONE pass over NVLink peer memory (the reference leaves it to ZeRO-3 / FSDP:
+    full-weight STE backward on every rank, then a reduce-scatter; quantization/qlinear.py:63-78):
+      1. `bdq_rows_push`: every rank stores the rows of its gradient (w.r.t. the fake-quantised weight) that belong to rank
+         r's dim-0 shard into r's symmetric-memory inbox -- the kernel's stores are the NVLink transfer, one launch per
+         parameter group;
+      2. one symmetric-memory barrier (the inbox is double-buffered across calls, like ShardGatherGroup's payload);
+      3. `bdq_int_ste_bwd_nsrc` per tensor: the STE backward of the shard with the incoming gradient summed on the fly from the
+         rank's own rows and the n-1 inbox slots, in rank order, one rounding to the dtype per addition (for two ranks: the
+         rounded exact sum, bit-equal to an NCCL reduce-scatter; in general what a ring reduction in that dtype computes).
+    The reduced gradient is never materialised.  `shapes`: [(rows, cols)] of the group's tensors."""
+
+    def __init__(self, shapes, group_size, dtype, device, group=None):
+        import torch.distributed._symmetric_memory as symm_mem
+        self.shapes, self.group_size, self.dtype, self.device, self.pg = list(shapes), group_size, dtype, torch.device(device), group
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        if not 2 <= self.world <= 8:
+            raise ValueError("ShardGradReducer needs 2..8 ranks")
+        es = torch.empty(0, dtype=dtype).element_size()
+        self.spans = [[row_shard(r, k, self.world) for k in range(self.world)] for r, _ in self.shapes]     # [tensor][rank] -> (r0, r1)
+        # byte offset of tensor t inside rank k's flat shard layout, and the size of that layout
+        self.off = [[0] * len(self.shapes) for _ in range(self.world)]
+        self.size = [0] * self.world
+        for k in range(self.world):
+            o = 0
+            for t, (_, c) in enumerate(self.shapes):
+                self.off[k][t] = o
+                o += (self.spans[t][k][1] - self.spans[t][k][0]) * c * es
+            self.size[k] = o
+        self.slot = (max(self.size) + 255) // 256 * 256                  # one source's rows of one rank's shard
+        self.half = (self.world - 1) * self.slot
+        self.inbox = symm_mem.empty(2 * self.half, dtype=torch.uint8, device=self.device)
+        self.hdl = symm_mem.rendezvous(self.inbox, self.pg if self.pg is not None else dist.group.WORLD)
+        self.ptrs = [int(p) for p in self.hdl.buffer_ptrs]
+        self.flip = 0
+        self.es = es
+
+    def _slot_of(self, src, dst):
+        """Index of source rank `src` among the n-1 inbox slots of rank `dst`."""
+        return src if src < dst else src - 1
+
+    @torch.no_grad()
+    def push(self, g_fulls):
+        """Stage 1 + 2 on the reducer's own stream (so that the NVLink transfer of one parameter group overlaps the HBM-bound
+        STE backward of the previous one): push this rank's rows to their owners, then the barrier.  Returns a ticket for
+        `finish`.  Calls must alternate push / finish per group, at most one push ahead."""
+        import ctypes
+
+        from . import _lib as L
+        if not hasattr(self, "comm"):
+            self.comm = torch.cuda.Stream(self.device)
+            self._done = None                 # event: the STE launches of the previous `finish` have completed
+        base = self.flip * self.half
+        self.flip ^= 1
+        me, n, es = self.rank, self.world, self.es
+        src, dst, nb = [], [], []
+        gs = [g.contiguous() for g in g_fulls]
+        for t, ((_, c), g) in enumerate(zip(self.shapes, gs)):
+            L.require_cuda(g)
+            assert g.dtype == self.dtype and tuple(g.shape) == tuple(self.shapes[t])
+            for k in range(n):
+                if k == me:
+                    continue
+                r0, r1 = self.spans[t][k]
+                if r1 > r0:
+                    src.append(g.data_ptr() + r0 * c * es)
+                    dst.append(self.ptrs[k] + base + self._slot_of(me, k) * self.slot + self.off[k][t])
+                    nb.append((r1 - r0) * c * es)
+        m = len(src)
+        cur = torch.cuda.current_stream(self.device)
+        self.comm.wait_stream(cur)               # the gradients were produced on the caller's stream
+        with torch.cuda.device(self.device), torch.cuda.stream(self.comm):
+            rc = L.lib().bdq_rows_push(m, (ctypes.c_void_p * max(m, 1))(*src), (ctypes.c_void_p * max(m, 1))(*dst),
+                                       (ctypes.c_int64 * max(m, 1))(*nb), L.stream_ptr(self.device))
+            L.check(rc, "bdq_rows_push")
+            # passing this barrier tells every peer that this rank is done READING the inbox half the peers write next:
+            # wait for the previous group's STE launches (they read the other half, which the next push overwrites)
+            if self._done is not None:
+                self.comm.wait_event(self._done)
+            self.hdl.barrier(channel=1)          # every rank's rows have landed in this rank's inbox
+            landed = torch.cuda.Event()
+            landed.record(self.comm)
+        return (base, gs, landed)
+
+    @torch.no_grad()
+    def finish(self, ticket, shards, outs=None):
+        """Stage 3 on the caller's stream: the multi-source STE backward of every tensor of the group."""
+        import ctypes
+
+        from . import _lib as L
+        base, gs, landed = ticket
+        me, n, es = self.rank, self.world, self.es
+        cur = torch.cuda.current_stream(self.device)
+        cur.wait_event(landed)
+        st = L.stream_ptr(self.device)
+        res = []
+        with torch.cuda.device(self.device):
+            for t, ((_, c), w, g) in enumerate(zip(self.shapes, shards, gs)):
+                r0, r1 = self.spans[t][me]
+                w = w.detach().contiguous()
+                gw = torch.empty_like(w) if outs is None else outs[t]
+                srcs = []
+                for k in range(n):               # rank order: every shard is reduced in the same order as an all-reduce would
+                    if k == me:
+                        srcs.append(g.data_ptr() + r0 * c * es)
+                    else:
+                        srcs.append(self.inbox.data_ptr() + base + self._slot_of(k, me) * self.slot + self.off[me][t])
+                rc = L.lib().bdq_int_ste_bwd_nsrc(L.ptr(w), n, (ctypes.c_void_p * n)(*srcs), L.ptr(gw), L.i64(w.numel()),
+                                                  int(self.group_size), 2, L.dtype_code(w), L.semantics(), st)
+                L.check(rc, "bdq_int_ste_bwd_nsrc")
+                res.append(gw)
+        self._done = torch.cuda.Event()
+        self._done.record(cur)
+        for g in gs:                             # pushed on the reducer's stream: keep the allocator from reusing them early
+            g.record_stream(self.comm)
+        return res
+
+    def backward(self, shards, g_fulls, outs=None):
+        """shards[t]: this rank's rows of weight t; g_fulls[t]: this rank's [rows, cols] gradient w.r.t. the fake-quantised
+        weight t.  Returns the gradients of the shards (written into `outs` if given)."""
+        return self.finish(self.push(g_fulls), shards, outs)

@@ -72,6 +72,21 @@ int bdq_int_ste_bwd(const void* w, const void* gy, void* gw, int64_t n_elem, int
                     int sem, bdq_stream_t stream);
 
 /*
+ * Fused reduce-scatter + STE backward for FSDP2 shards (no reference counterpart: under ZeRO-3 / FSDP the reference runs the
+ * STE backward on the full weight on every rank and leaves the reduce-scatter to the framework, quantization/qlinear.py:63-78).
+ * The STE backward is linear in the incoming gradient and group-local, so it commutes with the sum over ranks:
+ *   bdq_rows_push        copies up to 64 contiguous segments per launch; with peer-mapped destinations (symmetric memory) every
+ *                        rank pushes the rows of its gradient that belong to rank r's shard into r's inbox over NVLink
+ *                        (src / dst / nbytes are HOST arrays; 32-byte aligned, multiples of 32 bytes)
+ *   bdq_int_ste_bwd_nsrc bdq_int_ste_bwd whose incoming gradient is gy[0] + gy[1] + ... + gy[nsrc-1] (1..8 device pointers in a
+ *                        HOST array), accumulated in that order with one rounding to the tensor dtype per addition; 16-bit
+ *                        dtypes, bits 2/3, group 32/64/128.  The reduced gradient is never materialised.
+ */
+int bdq_rows_push(int nseg, const void* const* src, void* const* dst, const int64_t* nbytes, bdq_stream_t stream);
+int bdq_int_ste_bwd_nsrc(const void* w, int nsrc, const void* const* gy, void* gw, int64_t n_elem, int group, int bits, int dtype,
+                         int sem, bdq_stream_t stream);
+
+/*
  * NF3 (8-level, two scales per group) fake-quant.  Replaces SteN2F3Quantizer.forward
  * (quantization/quantizer.py:189-242) and pseudo_quantize_n2f3_tensor (quantizer.py:113-116).
  * Optional: codes [n_elem] uint8 (0..4 positive level, 5..7 negative level 1..3, 255 NaN),

@@ -178,3 +178,53 @@ def test_errors():
     assert lib.bdq_int2_shard_encode(None, None, None, i64(128), 128, 1, 1, 0, 8, None, None, None) == -1
     assert lib.bdq_int2_shard_decode(None, None, None, i64(0), 128, 1, None) == 0
     assert lib.bdq_int2_shard_decode(None, None, None, i64(128), 128, 1, None) == -1
+
+
+@pytest.mark.parametrize("dname", ["bf16", "f16"])
+@pytest.mark.parametrize("nsrc", [2, 3, 8])
+def test_ste_bwd_multi_source_and_push(dname, nsrc):
+    """bdq_rows_push + bdq_int_ste_bwd_nsrc on one GPU: pushing row ranges into inbox slots and summing `nsrc` gradient
+    sources on the fly equals the sequential sum (one rounding per addition, source order) followed by bdq_int_ste_bwd,
+    bit for bit -- including groups that take the op-by-op path (huge dynamic range) and NaN gradients."""
+    import ctypes
+
+    from bitdistiller_b200 import _lib as L
+    dt = {"bf16": torch.bfloat16, "f16": torch.float16}[dname]
+    dev = torch.device("cuda:0")
+    rows, cols, G = 96, 1024, 128
+    g = torch.Generator().manual_seed(nsrc)
+    w = (torch.randn(rows, cols, generator=g) * 0.02).to(dt)
+    w[3, :128] *= 1e-6          # tiny group next to ...
+    w[3, 5] = 30000.0 if dname == "f16" else 3e30   # ... an extreme one: op-by-op path
+    w = w.to(dev)
+    srcs = [torch.randn(rows, cols, generator=g).to(dt).to(dev) for _ in range(nsrc)]
+    srcs[-1][7, 9] = float("nan")
+    # push every source but the first into "inbox" slots with bdq_rows_push (two segments per source: ragged split)
+    inbox = torch.zeros((nsrc - 1, rows, cols), dtype=dt, device=dev)
+    es = w.element_size()
+    src_p, dst_p, nb = [], [], []
+    for i in range(1, nsrc):
+        cut = 32 * i % rows or 32
+        for r0, r1 in ((0, cut), (cut, rows)):
+            src_p.append(srcs[i].data_ptr() + r0 * cols * es)
+            dst_p.append(inbox[i - 1].data_ptr() + r0 * cols * es)
+            nb.append((r1 - r0) * cols * es)
+    m = len(src_p)
+    st = L.stream_ptr(dev)
+    L.check(L.lib().bdq_rows_push(m, (ctypes.c_void_p * m)(*src_p), (ctypes.c_void_p * m)(*dst_p), (ctypes.c_int64 * m)(*nb), st), "push")
+    assert torch.equal(inbox.view(torch.int16), torch.stack(srcs[1:]).view(torch.int16))
+    gw = torch.empty_like(w)
+    ptrs = [srcs[0].data_ptr()] + [inbox[i].data_ptr() for i in range(nsrc - 1)]
+    L.check(L.lib().bdq_int_ste_bwd_nsrc(L.ptr(w), nsrc, (ctypes.c_void_p * nsrc)(*ptrs), L.ptr(gw), L.i64(w.numel()), G, 2,
+                                         L.dtype_code(w), L.semantics(), st), "nsrc")
+    acc = srcs[0].clone()
+    for s in srcs[1:]:
+        acc = (acc.float() + s.float()).to(dt)
+    ref = torch.empty_like(w)
+    L.check(L.lib().bdq_int_ste_bwd(L.ptr(w), L.ptr(acc), L.ptr(ref), L.i64(w.numel()), G, 2, L.dtype_code(w), L.semantics(), st), "bwd")
+    torch.cuda.synchronize()
+    same = (gw.view(torch.int16) == ref.view(torch.int16)) | (gw.isnan() & ref.isnan())
+    assert bool(same.all()), int((~same).sum())
+    with pytest.raises(L.BdqError):
+        L.check(L.lib().bdq_int_ste_bwd_nsrc(L.ptr(w), 9, (ctypes.c_void_p * 9)(*([ptrs[0]] * 9)), L.ptr(gw), L.i64(w.numel()), G, 2,
+                                             L.dtype_code(w), L.semantics(), st), "nsrc")
