@@ -545,6 +545,21 @@ def quantized_all_gather(w_shard, gatherer, average=False):
 
 
 # ------------------------------------------------------------------------------------------------- gradient push + fused STE
+def grad_inbox_layout(shapes, world, elem_size, multiple=16):
+    """Host-side layout of ShardGradReducer: spans[t][k] = rows of tensor t owned by rank k, off[k][t] = byte offset of tensor
+    t inside rank k's flat shard layout, size[k] = bytes of that layout, slot = bytes of one inbox slot (256-aligned max)."""
+    spans = [[row_shard(r, k, world, multiple) for k in range(world)] for r, _ in shapes]
+    off = [[0] * len(shapes) for _ in range(world)]
+    size = [0] * world
+    for k in range(world):
+        o = 0
+        for t, (_, c) in enumerate(shapes):
+            off[k][t] = o
+            o += (spans[t][k][1] - spans[t][k][0]) * c * elem_size
+        size[k] = o
+    return spans, off, size, (max(size) + 255) // 256 * 256
+
+
 class ShardGradReducer:
     """The backward half of the sharded QAT step as ONE pass over NVLink peer memory (the reference leaves it to ZeRO-3 / FSDP:
     full-weight STE backward on every rank, then a reduce-scatter; quantization/qlinear.py:63-78):
@@ -564,17 +579,7 @@ class ShardGradReducer:
         if not 2 <= self.world <= 8:
             raise ValueError("ShardGradReducer needs 2..8 ranks")
         es = torch.empty(0, dtype=dtype).element_size()
-        self.spans = [[row_shard(r, k, self.world) for k in range(self.world)] for r, _ in self.shapes]     # [tensor][rank] -> (r0, r1)
-        # byte offset of tensor t inside rank k's flat shard layout, and the size of that layout
-        self.off = [[0] * len(self.shapes) for _ in range(self.world)]
-        self.size = [0] * self.world
-        for k in range(self.world):
-            o = 0
-            for t, (_, c) in enumerate(self.shapes):
-                self.off[k][t] = o
-                o += (self.spans[t][k][1] - self.spans[t][k][0]) * c * es
-            self.size[k] = o
-        self.slot = (max(self.size) + 255) // 256 * 256                  # one source's rows of one rank's shard
+        self.spans, self.off, self.size, self.slot = grad_inbox_layout(self.shapes, self.world, es)
         self.half = (self.world - 1) * self.slot
         self.inbox = symm_mem.empty(2 * self.half, dtype=torch.uint8, device=self.device)
         self.hdl = symm_mem.rendezvous(self.inbox, self.pg if self.pg is not None else dist.group.WORLD)

@@ -132,3 +132,26 @@ def test_shard_gather_group_offsets_partition_the_buffer():
     for v, (r, c) in zip(g.views, shapes):
         assert v.data_ptr() == g.flat.data_ptr() + 2 * off
         off += r * c
+
+
+def test_grad_inbox_layout_host_logic():
+    """ShardGradReducer's host-side layout: every rank's flat shard layout tiles the tensors without gaps, ragged shards
+    included, and the n-1 inbox slots of a rank are addressed consistently by sender and receiver."""
+    from bitdistiller_b200.sharded import grad_inbox_layout, row_shard
+    shapes = [(4096, 4096), (11008, 4096), (4096, 11008), (48, 256)]
+    for world in (2, 3, 8):
+        spans, off, size, slot = grad_inbox_layout(shapes, world, 2)
+        for t, (r, c) in enumerate(shapes):
+            assert [s for s in spans[t]] == [row_shard(r, k, world) for k in range(world)]
+            assert spans[t][0][0] == 0 and spans[t][-1][1] == r
+            assert all(spans[t][k][1] == spans[t][k + 1][0] for k in range(world - 1))
+        for k in range(world):
+            o = 0
+            for t, (r, c) in enumerate(shapes):
+                assert off[k][t] == o and o % 32 == 0
+                o += (spans[t][k][1] - spans[t][k][0]) * c * 2
+            assert size[k] == o <= slot and slot % 256 == 0
+        assert sum(size) == sum(r * c * 2 for r, c in shapes)
+        # sender `s` writes slot index (s if s < d else s - 1) of receiver d: the n-1 senders of d get distinct slots 0..n-2
+        for d in range(world):
+            assert sorted((s if s < d else s - 1) for s in range(world) if s != d) == list(range(world - 1))
