@@ -15,9 +15,9 @@ case "$cmd" in
     n=${1:-2}
     python -m torch.distributed.run --nnodes=1 --nproc-per-node "$n" --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus "$n" \
       --steps 5 --warmup 3 > "gpurun_out/bench_n$n.json" 2> "gpurun_out/bench_n$n.err"; tail -c 3000 "gpurun_out/bench_n$n.json"; tail -3 "gpurun_out/bench_n$n.err" ;;
-  launches)     # ncu launch list of the bench command (shares of the step, not absolutes)
+  launches)     # ncu launch list of the bench command: the 128 bdq:: launches of the 2 timed steps (3 warm-up steps skipped)
     python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/plain.log 2>&1 &&
-    ncu --metrics gpu__time_duration.sum --clock-control none -s 200 -c 200 --csv --log-file gpurun_out/launches.csv \
+    ncu --metrics gpu__time_duration.sum --clock-control none -k "regex:int_thr" -s 192 -c 128 --csv --log-file gpurun_out/launches.csv \
       python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/ncu.log 2>&1; tail -3 gpurun_out/ncu.log ;;
   ncu)          # one --set full capture: bash tools/gpu_check.sh ncu <kernel regex> <out name> <python script + args>
     pat=$1; out=$2; shift 2
