@@ -372,3 +372,51 @@ extern "C" int bdq_rows_push(int nseg, const void* const* src, void* const* dst,
     }
     return BDQ_OK;
 }
+
+namespace bdq {
+struct PeerFlags {
+    unsigned int* flags[8];   // flags[r] = rank r's flag array (8 x u32), peer-mapped into this process
+};
+}  // namespace bdq
+
+// ---- cross-GPU barrier on peer-mapped flags --------------------------------------------------------------------------
+// One tiny kernel per barrier: lane k stores the epoch into slot [my rank] of rank k's flag array (peer-mapped, NVLink) with
+// system-scope release semantics, then spins on slot [k] of its own array until rank k's store of the same epoch arrives.
+// Epochs only grow, so the flags are never reset.  Stream order makes the kernel a barrier for the work around it: everything
+// this rank launched before it (e.g. the payload / gradient peer stores) has completed when its flags go out, and nothing
+// launched after it starts before every peer's flag has arrived.  Replaces torch symmetric memory's barrier on the hot path
+// (measured on 2 x B200: ~40 us per barrier there, a handful of microseconds here).
+namespace bdq {
+__global__ void __launch_bounds__(32) peer_barrier_kernel(const PeerFlags pf, int me, int n, unsigned int epoch) {
+    const int k = threadIdx.x;
+    if (k < n && k != me) {
+        __threadfence_system();
+        unsigned int* dst = pf.flags[k] + me;
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(dst), "r"(epoch) : "memory");
+        const unsigned int* src = pf.flags[me] + k;
+        unsigned int v;
+        do {
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(src) : "memory");
+        } while ((int)(v - epoch) < 0);   // wrap-safe: epochs are compared as a signed distance
+    }
+    __syncwarp();
+    __threadfence_system();
+}
+}  // namespace bdq
+
+extern "C" int bdq_peer_barrier(void* const* flags, int my_rank, int n_ranks, unsigned int epoch, bdq_stream_t stream) {
+    using namespace bdq;
+    if (!flags || n_ranks < 1 || n_ranks > 8 || my_rank < 0 || my_rank >= n_ranks) {
+        set_error("peer_barrier: 1..8 ranks, flags[n_ranks] required");
+        return BDQ_ERR_SHAPE;
+    }
+    PeerFlags pf;
+    memset(&pf, 0, sizeof(pf));
+    for (int i = 0; i < n_ranks; ++i) {
+        if (!flags[i] || ((uintptr_t)flags[i] % 4)) { set_error("peer_barrier: flags[%d] null or misaligned", i); return BDQ_ERR_ALIGN; }
+        pf.flags[i] = (unsigned int*)flags[i];
+    }
+    if (n_ranks == 1) return BDQ_OK;
+    peer_barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(pf, my_rank, n_ranks, epoch);
+    return check_launch("bdq_peer_barrier");
+}

@@ -279,6 +279,40 @@ def reduce_scatter_rows(g_full, layout, rank, group=None, average=False):
     return g
 
 
+class PeerBarrier:
+    """Cross-GPU barrier on flags in symmetric memory (bdq_peer_barrier: one 32-thread kernel, a few microseconds) instead of
+    torch symmetric memory's barrier (~40 us on 2 x B200).  BDQ_TORCH_BARRIER=1 keeps the torch barrier (A/B comparisons)."""
+
+    def __init__(self, device, group=None):
+        import os
+
+        import torch.distributed._symmetric_memory as symm_mem
+        self.device = torch.device(device)
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        self.buf = symm_mem.empty(64, dtype=torch.uint8, device=self.device)
+        self.buf.zero_()
+        self.hdl = symm_mem.rendezvous(self.buf, group if group is not None else dist.group.WORLD)
+        self.ptrs = [int(p) for p in self.hdl.buffer_ptrs]
+        self.epoch = 0
+        self.use_torch = os.environ.get("BDQ_TORCH_BARRIER", "0") == "1"
+        torch.cuda.synchronize(self.device)
+        self.hdl.barrier(channel=0)          # every rank's flags are zero before the first epoch goes out
+        torch.cuda.synchronize(self.device)
+
+    def __call__(self):
+        import ctypes
+
+        from . import _lib as L
+        if self.use_torch:
+            self.hdl.barrier(channel=0)
+            return
+        self.epoch += 1
+        with torch.cuda.device(self.device):
+            rc = L.lib().bdq_peer_barrier((ctypes.c_void_p * self.world)(*self.ptrs), self.rank, self.world,
+                                          ctypes.c_uint32(self.epoch & 0xffffffff), L.stream_ptr(self.device))
+        L.check(rc, "bdq_peer_barrier")
+
+
 class ShardGather:
     """Quantise-before-all-gather of ONE int2 QLinear weight [rows, cols] held as dim-0 shards (FSDP2 layout):
     `forward(w_shard)` returns the fake-quantised FULL weight on every rank, bit-equal to
@@ -401,6 +435,7 @@ class ShardGatherGroup:
             self.ptrs2 = [int(p) for p in self.hdl.buffer_ptrs]
             self.flip = 0
             self._select(0)
+            self.barrier = PeerBarrier(self.device, self.pg)
         else:
             self.buf = torch.empty(co + so, dtype=torch.uint8, device=self.device)
             self.ptrs = [self.buf.data_ptr()]
@@ -453,7 +488,7 @@ class ShardGatherGroup:
             self._select(self.flip)
             self.flip ^= 1
             self._encode_all(shards)
-            self.hdl.barrier(channel=0)
+            self.barrier()
         else:
             self._encode_all(shards)
             if self.world > 1:                       # collective transport: per tensor, ragged slots padded
@@ -586,6 +621,7 @@ class ShardGradReducer:
         self.ptrs = [int(p) for p in self.hdl.buffer_ptrs]
         self.flip = 0
         self.es = es
+        self.barrier = PeerBarrier(self.device, self.pg)
 
     def _slot_of(self, src, dst):
         """Index of source rank `src` among the n-1 inbox slots of rank `dst`."""
@@ -629,7 +665,7 @@ class ShardGradReducer:
             # wait for the previous group's STE launches (they read the other half, which the next push overwrites)
             if self._done is not None:
                 self.comm.wait_event(self._done)
-            self.hdl.barrier(channel=1)          # every rank's rows have landed in this rank's inbox
+            self.barrier()                       # every rank's rows have landed in this rank's inbox
             landed = torch.cuda.Event()
             landed.record(self.comm)
         return (base, gs, landed)

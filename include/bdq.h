@@ -82,6 +82,12 @@ int bdq_int_ste_bwd(const void* w, const void* gy, void* gw, int64_t n_elem, int
  *                        HOST array), accumulated in that order with one rounding to the tensor dtype per addition; 16-bit
  *                        dtypes, bits 2/3, group 32/64/128.  The reduced gradient is never materialised.
  */
+/*
+ * Cross-GPU barrier on peer-mapped flags (one 32-thread kernel): flags[r] = rank r's array of 8 uint32 (symmetric memory, zeroed
+ * once), `epoch` = 1, 2, 3, ... identical on all ranks for the same barrier.  Stream-ordered: the rank's earlier work (e.g. its
+ * NVLink peer stores) has completed when its flags go out; later work starts after every peer's flag of this epoch has arrived.
+ */
+int bdq_peer_barrier(void* const* flags, int my_rank, int n_ranks, unsigned int epoch, bdq_stream_t stream);
 int bdq_rows_push(int nseg, const void* const* src, void* const* dst, const int64_t* nbytes, bdq_stream_t stream);
 int bdq_int_ste_bwd_nsrc(const void* w, int nsrc, const void* const* gy, void* gw, int64_t n_elem, int group, int bits, int dtype,
                          int sem, bdq_stream_t stream);
