@@ -437,3 +437,224 @@ bool launch_nf3_thr_bwd(const void* w, const void* gy, void* gw, int64_t n, int 
 }
 
 }  // namespace bdq
+
+// ================================================================================================ NF3 shard payload
+// Quantise-before-all-gather for NF3 (QLinear's class default quant_type is "ste-n2f3", quantization/qlinear.py:51): the
+// owner of a dim-0 shard quantises it once and ships 3-bit level indices + the two scales of every group -- 0.40625 B/weight
+// at group 128 instead of 2 -- and every rank rebuilds  dq = rT(lvl[e] * s)  (s = sp for e >= 3, sn for e < 3), the forward's
+// own last operation, so the result is bit-equal to SteN2F3Quantizer.forward on the gathered weight.
+// Wire format (this build's own): per 32 consecutive elements three uint32 words (lo0, lo1, hi) = the packed-NF3 split of
+// nf3_packed.cu (bits [2j, 2j+2) of lo(j / 16) = low two bits of the staircase index e of element j, bit j of hi = its high
+// bit); per group one (sp, sn) pair of T values.  A group whose max or min is exactly 0 (the reference's 0/0: the whole group
+// is NaN) ships NaN scales.
+namespace bdq {
+
+constexpr int kNf3MaxDst = 8;
+struct Nf3Dst {
+    uint8_t* codes[kNf3MaxDst];
+    uint8_t* sc[kNf3MaxDst];
+    int n;
+};
+
+__device__ __forceinline__ uint32_t nf3_code_to_stair(int c) { return c == 0 ? 3u : (c <= 4 ? (uint32_t)c + 3u : 7u - (uint32_t)c); }
+
+// op-by-op level indices of one lane's 32 elements (groups whose thresholds could not be verified)
+template <int DT>
+__device__ __noinline__ uint3 nf3_encode_slow_global(const void* w, int64_t e0, float mx, float mn, const Nf3Tables& t) {
+    const Nf3Q p = nf3_group_params(mx, mn);
+    uint32_t lo[2] = {0u, 0u}, hi = 0u;
+#pragma unroll 1
+    for (int j = 0; j < 32; ++j) {
+        float q, y;
+        int code;
+        nf3_elem<DT>(load_scalar<DT>(w, e0 + j), p, t, q, y, code);
+        const uint32_t e = code > 7 ? 3u : nf3_code_to_stair(code);
+        lo[j >> 4] |= (e & 3u) << (2 * (j & 15));
+        hi |= (e >> 2) << j;
+    }
+    return make_uint3(lo[0], lo[1], hi);
+}
+
+template <int DT, int G>
+__global__ void __launch_bounds__(kNf3ThrThreads) nf3_shard_encode_kernel(const uint8_t* __restrict__ w, Nf3Dst dst, int64_t nchunk,
+                                                                          const __grid_constant__ Nf3Tables tab,
+                                                                          const __grid_constant__ Nf3Stair st) {
+    using P = P2<DT>;
+    constexpr int LPG = G / 32;
+    constexpr int R = (7 + LPG - 1) / LPG;
+    constexpr int NP = (R + 1) / 2;
+    const int lane = threadIdx.x & 31;
+    const int lig = lane & (LPG - 1);
+    const int gbase = lane & ~(LPG - 1);
+    const int64_t warp = (int64_t)blockIdx.x * (kNf3ThrThreads / 32) + (threadIdx.x >> 5);
+    const int64_t nwarps = (int64_t)gridDim.x * (kNf3ThrThreads / 32);
+    const int64_t nwc = (nchunk + 31) / 32;
+    Nf3Step my[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) my[r] = st.k[lig + r * LPG];
+    // "value" of level c for the select = its index, laid out so that one shift + or puts both elements of a pair side by
+    // side: low half (c & 3) | (c >> 2) << 8, high half (c & 3) | (c >> 2) << 7
+    uint32_t v2e[8];
+#pragma unroll
+    for (int c = 0; c < 8; ++c) v2e[c] = ((uint32_t)(c & 3) | ((uint32_t)(c >> 2) << 8)) | (((uint32_t)(c & 3) | ((uint32_t)(c >> 2) << 7)) << 16);
+    for (int64_t wc = warp; wc < nwc; wc += nwarps) {
+        const int64_t idx = wc * 32 + lane;
+        const bool valid = idx < nchunk;
+        U8 raw[2];
+        if (valid) {
+            raw[0] = ldg256(w + idx * 64);
+            raw[1] = ldg256(w + idx * 64 + 32);
+        } else {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) raw[0].r[i] = raw[1].r[i] = 0;
+        }
+        float mx, mn, mx1, mn1;
+        vec_minmax16<DT>(raw[0], mx, mn);
+        vec_minmax16<DT>(raw[1], mx1, mn1);
+        mx = group_max<LPG>(fmaxf(mx, mx1));
+        mn = group_min<LPG>(fminf(mn, mn1));
+        const float sp = fabsf(mx), sn = fabsf(mn);
+        uint32_t sh[LPG][NP];
+        const bool ok = nf3_group_thresholds<DT, LPG>(my, st.mask, sp, sn, lig, gbase, sh);
+        const uint32_t okm = __ballot_sync(0xffffffffu, ok);
+        const uint32_t gm = nf3_group_lane_mask<LPG>(lane);
+        uint3 cw = make_uint3(0u, 0u, 0u);
+        if ((okm & gm) == gm) {
+            uint32_t lo[2], hi = 0u;
+#pragma unroll
+            for (int v = 0; v < 2; ++v) {
+                uint32_t la = 0u, ha = 0u;
+#pragma unroll
+                for (int i = 7; i >= 0; --i) {
+                    const uint32_t r = nf3_select<DT, LPG>(raw[v].r[i], sh, v2e);
+                    const uint32_t u = r | (r >> 14);          // bits 0-3: low codes of the pair, bits 8-9: their high bits
+                    la = la * 16u + (u & 0xFu);
+                    ha = ha * 4u + ((u >> 8) & 3u);
+                }
+                lo[v] = la;
+                hi |= ha << (16 * v);
+            }
+            cw = make_uint3(lo[0], lo[1], hi);
+        } else if (valid) {
+            cw = nf3_encode_slow_global<DT>(w, idx * 32, mx, mn, tab);
+        }
+        if (valid) {
+            const bool nan_group = (sp == 0.f) || (sn == 0.f) || (sp != sp) || (sn != sn);
+            const float qnan = __int_as_float(0x7fc00000);
+            const uint32_t scp = P::bits(P::pack(nan_group ? qnan : sp, nan_group ? qnan : sn));
+            const int64_t g = idx / LPG;
+#pragma unroll 1
+            for (int d = 0; d < dst.n; ++d) {
+                uint32_t* cp = reinterpret_cast<uint32_t*>(dst.codes[d] + idx * 12);
+                cp[0] = cw.x;
+                cp[1] = cw.y;
+                cp[2] = cw.z;
+                if (lig == 0) *reinterpret_cast<uint32_t*>(dst.sc[d] + g * 4) = scp;
+            }
+        }
+    }
+}
+
+template <int DT, int G>
+__global__ void __launch_bounds__(kNf3ThrThreads) nf3_shard_decode_kernel(const uint8_t* __restrict__ codes, const uint8_t* __restrict__ sc,
+                                                                          uint8_t* __restrict__ dq, int64_t nchunk,
+                                                                          const __grid_constant__ Nf3Stair st) {
+    using P = P2<DT>;
+    using h2 = typename P::h2;
+    constexpr int LPG = G / 32;
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = (int64_t)blockIdx.x * (kNf3ThrThreads / 32) + (threadIdx.x >> 5);
+    const int64_t nwarps = (int64_t)gridDim.x * (kNf3ThrThreads / 32);
+    const int64_t nwc = (nchunk + 31) / 32;
+    for (int64_t wc = warp; wc < nwc; wc += nwarps) {
+        const int64_t idx = wc * 32 + lane;
+        if (idx >= nchunk) continue;
+        const uint32_t* cp = reinterpret_cast<const uint32_t*>(codes + idx * 12);
+        const uint32_t lo[2] = {__ldg(cp), __ldg(cp + 1)}, hi = __ldg(cp + 2);
+        const h2 scp = P::from_bits(__ldg(reinterpret_cast<const uint32_t*>(sc + (idx / LPG) * 4)));
+        const h2 s2p = P::dup_lo(scp), s2n = P::dup_hi(scp);
+        // the group's 8 output values rT(lvl * s) as a 16-byte table (v0,v1) (v2,v3) (v4,v5) (v6,v7); level 3 is exactly 0
+        // unless the group is NaN (0 * NaN)
+        uint32_t tb[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const h2 a = __hmul2(P::from_bits(st.lvl2[2 * j]), (2 * j) < 3 ? s2n : s2p);
+            const h2 b = __hmul2(P::from_bits(st.lvl2[2 * j + 1]), (2 * j + 1) < 3 ? s2n : s2p);
+            tb[j] = (P::bits(a) & 0xffffu) | (P::bits(b) & 0xffff0000u);
+        }
+        U8 out[2];
+#pragma unroll
+        for (int v = 0; v < 2; ++v)
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const uint32_t t4 = (lo[v] >> (4 * i)) & 0xFu;                   // low codes of elements 2i, 2i+1
+                const uint32_t sel = 0x1010u + (t4 & 3u) * 0x22u + (t4 >> 2) * 0x2200u;   // byte selectors of the two halfwords
+                const uint32_t x = __byte_perm(tb[0], tb[1], sel), y = __byte_perm(tb[2], tb[3], sel);
+                const uint32_t hb = (hi >> (16 * v + 2 * i)) & 3u;
+                const uint32_t m = (hb & 1u) * 0xffffu + (hb >> 1) * 0xffff0000u;
+                out[v].r[i] = (x & ~m) | (y & m);
+            }
+        stg256(dq + idx * 64, out[0]);
+        stg256(dq + idx * 64 + 32, out[1]);
+    }
+}
+
+static int64_t nf3_shard_blocks(int64_t nchunk) { return ((nchunk + 31) / 32 + (kNf3ThrThreads / 32) - 1) / (kNf3ThrThreads / 32); }
+
+}  // namespace bdq
+
+using namespace bdq;
+
+static int nf3_shard_check(int64_t n_elem, int group, int dtype) {
+    if (dtype != BDQ_BF16 && dtype != BDQ_F16) { set_error("nf3 shard: dtype must be bf16 or fp16"); return BDQ_ERR_DTYPE; }
+    if (group != 32 && group != 64 && group != 128) { set_error("nf3 shard: group must be 32, 64 or 128"); return BDQ_ERR_UNSUPPORTED; }
+    if (n_elem < 0 || n_elem % group != 0) { set_error("nf3 shard: n_elem=%lld is not a multiple of group=%d", (long long)n_elem, group); return BDQ_ERR_SHAPE; }
+    return BDQ_OK;
+}
+
+extern "C" int bdq_nf3_shard_encode(const void* w, void* codes, void* scales, int64_t n_elem, int group, int dtype, int sem, int n_peer,
+                                    void* const* peer_codes, void* const* peer_scales, bdq_stream_t stream) {
+    int rc = nf3_shard_check(n_elem, group, dtype);
+    if (rc) return rc;
+    if (n_peer < 0 || n_peer > kNf3MaxDst - 1) { set_error("nf3 shard encode: n_peer=%d, at most %d", n_peer, kNf3MaxDst - 1); return BDQ_ERR_SHAPE; }
+    if (n_elem == 0) return BDQ_OK;
+    if (!w || !codes || !scales || (n_peer > 0 && (!peer_codes || !peer_scales))) { set_error("null tensor pointer"); return BDQ_ERR_SHAPE; }
+    if ((uintptr_t)w % 32) { set_error("nf3 shard encode: w must be 32-byte aligned"); return BDQ_ERR_ALIGN; }
+    Nf3Dst dst;
+    dst.n = 1 + n_peer;
+    dst.codes[0] = (uint8_t*)codes;
+    dst.sc[0] = (uint8_t*)scales;
+    for (int i = 0; i < n_peer; ++i) { dst.codes[1 + i] = (uint8_t*)peer_codes[i]; dst.sc[1 + i] = (uint8_t*)peer_scales[i]; }
+    for (int d = 0; d < dst.n; ++d)
+        if (!dst.codes[d] || !dst.sc[d] || ((uintptr_t)dst.codes[d] % 4) || ((uintptr_t)dst.sc[d] % 4)) {
+            set_error("nf3 shard encode: destination %d null or misaligned (4 B)", d);
+            return BDQ_ERR_ALIGN;
+        }
+    const Nf3Tables tab = make_tables(dtype, sem);
+    const Nf3Stair stair = make_stair(tab, dtype);
+    const int64_t nchunk = n_elem / 32, nb = nf3_shard_blocks(nchunk);
+    cudaStream_t st = (cudaStream_t)stream;
+    const uint8_t* wp = (const uint8_t*)w;
+#define BDQ_L(DT, GG) nf3_shard_encode_kernel<DT, GG><<<wave_grid(nf3_shard_encode_kernel<DT, GG>, kNf3ThrThreads, nb, 6), kNf3ThrThreads, 0, st>>>(wp, dst, nchunk, tab, stair)
+    if (dtype == BDQ_BF16) { if (group == 128) BDQ_L(kBF16, 128); else if (group == 64) BDQ_L(kBF16, 64); else BDQ_L(kBF16, 32); }
+    else { if (group == 128) BDQ_L(kF16, 128); else if (group == 64) BDQ_L(kF16, 64); else BDQ_L(kF16, 32); }
+#undef BDQ_L
+    return check_launch("bdq_nf3_shard_encode");
+}
+
+extern "C" int bdq_nf3_shard_decode(const void* codes, const void* scales, void* dq, int64_t n_elem, int group, int dtype,
+                                    bdq_stream_t stream) {
+    int rc = nf3_shard_check(n_elem, group, dtype);
+    if (rc) return rc;
+    if (n_elem == 0) return BDQ_OK;
+    if (!codes || !scales || !dq) { set_error("null tensor pointer"); return BDQ_ERR_SHAPE; }
+    if (((uintptr_t)dq % 32) || ((uintptr_t)codes % 4) || ((uintptr_t)scales % 4)) { set_error("nf3 shard decode: misaligned pointer (dq 32 B, payload 4 B)"); return BDQ_ERR_ALIGN; }
+    const Nf3Stair stair = make_stair(make_tables(dtype, 0), dtype);
+    const int64_t nchunk = n_elem / 32, nb = nf3_shard_blocks(nchunk);
+    cudaStream_t st = (cudaStream_t)stream;
+#define BDQ_L(DT, GG) nf3_shard_decode_kernel<DT, GG><<<wave_grid(nf3_shard_decode_kernel<DT, GG>, kNf3ThrThreads, nb, 16), kNf3ThrThreads, 0, st>>>((const uint8_t*)codes, (const uint8_t*)scales, (uint8_t*)dq, nchunk, stair)
+    if (dtype == BDQ_BF16) { if (group == 128) BDQ_L(kBF16, 128); else if (group == 64) BDQ_L(kBF16, 64); else BDQ_L(kBF16, 32); }
+    else { if (group == 128) BDQ_L(kF16, 128); else if (group == 64) BDQ_L(kF16, 64); else BDQ_L(kF16, 32); }
+#undef BDQ_L
+    return check_launch("bdq_nf3_shard_decode");
+}

@@ -83,6 +83,20 @@ int bdq_int_ste_bwd(const void* w, const void* gy, void* gw, int64_t n_elem, int
  *                        dtypes, bits 2/3, group 32/64/128.  The reduced gradient is never materialised.
  */
 /*
+ * NF3 payload for quantise-before-all-gather (QLinear's class default quant_type is "ste-n2f3", quantization/qlinear.py:51;
+ * no reference counterpart for the wire format).  bdq_nf3_shard_encode quantises a dim-0 shard (whole groups) and stores, into its
+ * own slot and into up to 7 peer-mapped slots, per 32 consecutive elements three uint32 words (lo0, lo1, hi: bits [2j, 2j+2) of
+ * lo(j / 16) = low two bits of the level index e of element j, bit j of hi = its high bit; e = position in the ascending staircase
+ * -1, -0.535, -0.247, 0, 0.183, 0.382, 0.623, 1) and per group one (|max|, |min|) pair of T values (NaN for a group whose max or
+ * min is exactly 0: the reference's 0/0).  bdq_nf3_shard_decode rebuilds dq = rT(level * scale), bit-equal to
+ * SteN2F3Quantizer.forward (quantization/quantizer.py:184-242) on the same weights.  16-bit dtypes, group 32/64/128;
+ * 0.40625 B/weight at group 128.
+ */
+int bdq_nf3_shard_encode(const void* w, void* codes, void* scales, int64_t n_elem, int group, int dtype, int sem, int n_peer,
+                         void* const* peer_codes, void* const* peer_scales, bdq_stream_t stream);
+int bdq_nf3_shard_decode(const void* codes, const void* scales, void* dq, int64_t n_elem, int group, int dtype, bdq_stream_t stream);
+
+/*
  * Cross-GPU barrier on peer-mapped flags (one 32-thread kernel): flags[r] = rank r's array of 8 uint32 (symmetric memory, zeroed
  * once), `epoch` = 1, 2, 3, ... identical on all ranks for the same barrier.  Stream-ordered: the rank's earlier work (e.g. its
  * NVLink peer stores) has completed when its flags go out; later work starts after every peer's flag of this epoch has arrived.

@@ -228,3 +228,54 @@ def test_ste_bwd_multi_source_and_push(dname, nsrc):
     with pytest.raises(L.BdqError):
         L.check(L.lib().bdq_int_ste_bwd_nsrc(L.ptr(w), 9, (ctypes.c_void_p * 9)(*([ptrs[0]] * 9)), L.ptr(gw), L.i64(w.numel()), G, 2,
                                              L.dtype_code(w), L.semantics(), st), "nsrc")
+
+
+@pytest.mark.parametrize("dname", ["bf16", "f16"])
+@pytest.mark.parametrize("G", [128, 64, 32])
+def test_nf3_shard_payload_roundtrip(dname, G):
+    """bdq_nf3_shard_encode / _decode (the NF3 payload of quantise-before-all-gather): level indices against the oracle's NF3
+    codes, scales against its (|max|, |min|), and decode(encode(w)) bit-equal to the NF3 fake-quantiser forward -- incl. the
+    groups that take the op-by-op path, the NaN groups (max or min exactly 0) and clipped (tie-heavy) weights."""
+    import ctypes
+
+    from bitdistiller_b200 import _lib as L
+    from bitdistiller_b200 import quantizer as Q
+    from bitdistiller_b200.sharded import ShardGatherNF3
+    dt = DT[dname]
+    rows, cols = 64, 1024
+    w = make_weight("randn", rows, cols, dt, 5)
+    lim = w.float().reshape(rows, -1, G).abs().amax(-1, keepdim=True) * 0.8
+    w[:16] = torch.clamp(w[:16].float().reshape(16, -1, G), -lim[:16], lim[:16]).reshape(16, cols).to(dt)   # ties at the extremes
+    w[20, :G] = w[20, :G].abs()
+    w[20, 3] = 0.0                      # min exactly 0 -> NaN group in the reference
+    w[21, :G] = 0.0                     # all-zero group
+    w[22, :G] *= 1e-6                   # tiny scales: op-by-op path
+    w[23, 5] = 3e4 if dname == "f16" else 3e30
+    wd = w.to(dev())
+    sg = ShardGatherNF3(rows, cols, G, dt, dev(), symmetric=False)
+    dq = sg.forward(wd)
+    ref_dq, sp, sn, codes = Q.nf3_fakequant(wd, G, want_codes=True, want_scales=True)
+    assert bits_equal(dq.cpu(), ref_dq.cpu())
+    orc = oracle.nf3_fakequant(w, G, sem=0)
+    assert bits_equal(dq.cpu(), orc["dq"])
+    # wire format: level index e per element from the three words of every 32-element chunk
+    words = sg.codes.cpu().numpy().view(np.uint32).reshape(-1, 3).astype(np.uint64)
+    j = np.arange(32)
+    lo = np.where(j[None, :] < 16, words[:, 0:1], words[:, 1:2])
+    e = ((lo >> (2 * (j % 16)).astype(np.uint64)[None, :]) & 3) | (((words[:, 2:3] >> j.astype(np.uint64)[None, :]) & 1) << 2)
+    e = e.reshape(rows, cols)
+    oc = orc["codes"].numpy().astype(np.int64)          # 0 = zero, 1..4 = positive levels, 5..7 = negative levels, 255 = NaN group
+    stair = np.where(oc == 0, 3, np.where(oc <= 4, oc + 3, 7 - oc))
+    ok = oc != 255
+    assert np.array_equal(e[ok], stair[ok])
+    sc = sg.sc.view(torch.int16).cpu().view(dt).float().reshape(rows, cols // G, 2)
+    nan_g = torch.from_numpy(~ok).reshape(rows, cols // G, G).any(-1)
+    assert bool(sc[nan_g].isnan().all())
+    assert torch.equal(sc[..., 0][~nan_g], sp.float().cpu().reshape(rows, -1)[~nan_g])
+    assert torch.equal(sc[..., 1][~nan_g], sn.float().cpu().reshape(rows, -1)[~nan_g])
+    # larger, through the flat layer launch shape
+    big = make_weight("heavy", 512, 4096, dt, 9).to(dev())
+    sgb = ShardGatherNF3(512, 4096, G, dt, dev(), symmetric=False)
+    assert bits_equal(sgb.forward(big).cpu(), Q.nf3_fakequant(big, G)[0].cpu())
+    with pytest.raises(L.BdqError):
+        L.check(L.lib().bdq_nf3_shard_decode(L.ptr(sgb.codes), L.ptr(sgb.sc), L.ptr(big), L.i64(100), G, L.dtype_code(big), L.stream_ptr(dev())), "x")

@@ -155,3 +155,13 @@ def test_grad_inbox_layout_host_logic():
         # sender `s` writes slot index (s if s < d else s - 1) of receiver d: the n-1 senders of d get distinct slots 0..n-2
         for d in range(world):
             assert sorted((s if s < d else s - 1) for s in range(world) if s != d) == list(range(world - 1))
+
+
+def test_nf3_payload_layout_host_logic():
+    from bitdistiller_b200.sharded import nf3_payload_layout
+    for world in (1, 2, 3, 8):
+        lay = nf3_payload_layout(11008, 4096, 128, world)
+        assert lay[0][0] == 0 and lay[-1][1] == 11008
+        assert sum(l[3] for l in lay) == 11008 * 4096 // 32 * 12 and sum(l[5] for l in lay) == 11008 * 32 * 4
+        for a, b in zip(lay, lay[1:]):
+            assert a[1] == b[0] and a[2] + a[3] == b[2] and a[4] + a[5] == b[4]
