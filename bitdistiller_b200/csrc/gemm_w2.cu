@@ -116,8 +116,12 @@ struct GemmPeers {   // tensor parallel: this rank's column slice inside the pee
     int n;
 };
 
-template <int MT>
+// BTMA = true: plain fp16 GEMM out = x @ W^T with W [OC, IC] fp16 row-major (bdq_gemm_f16): the B tile is a second TMA load
+// (box 64 k x 256 channels, the same K-major SWIZZLE_128B layout the dequant producers write), the producer warps only
+// run the epilogue.  Used for weight formats whose in-register decode is too expensive to hide behind the MMAs (packed NF3).
+template <int MT, bool BTMA>
 __global__ void __launch_bounds__(kGmThreads, 1) gemm_w2_kernel(const __grid_constant__ CUtensorMap xmap,
+                                                                const __grid_constant__ CUtensorMap wmap,
                                                                 const uint32_t* __restrict__ qweight,
                                                                 const __half* __restrict__ scales,
                                                                 const uint32_t* __restrict__ qzeros, __half* __restrict__ out,
@@ -142,12 +146,13 @@ __global__ void __launch_bounds__(kGmThreads, 1) gemm_w2_kernel(const __grid_con
     if (tid == 0) {
         for (int s = 0; s < kGmStages; ++s) {
             gm_mbar_init(&full_a[s], 1);
-            gm_mbar_init(&full_b[s], kGmN);
+            gm_mbar_init(&full_b[s], BTMA ? 1 : kGmN);
             gm_mbar_init(&empty[s], 1);
         }
         gm_mbar_init(tmem_full, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&xmap) : "memory");
+        if constexpr (BTMA) asm volatile("prefetch.tensormap [%0];" ::"l"(&wmap) : "memory");
     }
     if (warp == 1) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(gm_smem_u32(tmem_slot)), "r"(256 * MT) : "memory");
@@ -166,6 +171,10 @@ __global__ void __launch_bounds__(kGmThreads, 1) gemm_w2_kernel(const __grid_con
                 if (kb >= kGmStages) gm_mbar_wait(&empty[s], ((kb / kGmStages) - 1) & 1);
                 gm_mbar_expect_tx(&full_a[s], MT * kGmABytes);
                 gm_tma_load_2d(smem + s * kGmStageBytes, &xmap, kb * kGmK, m0, &full_a[s]);
+                if constexpr (BTMA) {
+                    gm_mbar_expect_tx(&full_b[s], kGmBBytes);
+                    gm_tma_load_2d(smem + s * kGmStageBytes + MT * kGmABytes, &wmap, kb * kGmK, n0, &full_b[s]);
+                }
             }
         }
     } else if (warp == 1) {
@@ -193,6 +202,7 @@ __global__ void __launch_bounds__(kGmThreads, 1) gemm_w2_kernel(const __grid_con
     } else {
         // ================= dequant producers: thread j <-> output channel n0 + j =================
         const int j = tid - 64;
+        if constexpr (!BTMA) {
         const int oc = min(n0 + j, OC - 1);   // a partial last tile re-reads the last channel; its columns are never stored
         const int wpr = IC >> 4;
         const uint32_t* wrow = qweight + (size_t)oc * wpr;
@@ -245,6 +255,8 @@ __global__ void __launch_bounds__(kGmThreads, 1) gemm_w2_kernel(const __grid_con
 #pragma unroll
             for (int h = 0; h < 2; ++h) { csc[h] = nsc[h]; czw[h] = nzw[h]; }
         }
+        }   // !BTMA
+        (void)j;
         // ================= epilogue: TMEM -> registers -> fp16 -> global =================
         gm_mbar_wait(tmem_full, 0);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -306,7 +318,8 @@ static EncodeTiledFn get_encode_tiled() {
 }
 
 int launch_gemm_w2(const void* x, const int32_t* qweight, const void* scales, const int32_t* qzeros, void* out, int64_t M,
-                   int64_t IC, int64_t OC, int group, int zw, cudaStream_t st, int64_t ldo, int n_peer, void* const* peer_out) {
+                   int64_t IC, int64_t OC, int group, int zw, cudaStream_t st, int64_t ldo, int n_peer, void* const* peer_out,
+                   const void* w_f16 = nullptr) {
     GemmPeers peers;
     memset(&peers, 0, sizeof(peers));
     peers.n = n_peer;
@@ -325,19 +338,30 @@ int launch_gemm_w2(const void* x, const int32_t* qweight, const void* scales, co
                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) { set_error("gemm_w2: cuTensorMapEncodeTiled failed (%d)", (int)r); return BDQ_ERR_CUDA; }
-    if (!ensure_dyn_smem(reinterpret_cast<const void*>(gemm_w2_kernel<1>), GmCfg<1>::kSmem) ||
-        !ensure_dyn_smem(reinterpret_cast<const void*>(gemm_w2_kernel<2>), GmCfg<2>::kSmem))
+    CUtensorMap wmap;
+    memset(&wmap, 0, sizeof(wmap));
+    if (w_f16) {   // plain fp16 weights [OC, IC]: B tiles by TMA
+        const cuuint64_t wd[2] = {(cuuint64_t)IC, (cuuint64_t)OC};
+        const cuuint64_t ws[1] = {(cuuint64_t)IC * 2};
+        const cuuint32_t wb[2] = {(cuuint32_t)kGmK, (cuuint32_t)kGmN};
+        r = enc(&wmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(w_f16), wd, ws, wb, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) { set_error("gemm_f16: cuTensorMapEncodeTiled failed (%d)", (int)r); return BDQ_ERR_CUDA; }
+    }
+    if (!ensure_dyn_smem(reinterpret_cast<const void*>(gemm_w2_kernel<1, false>), GmCfg<1>::kSmem) ||
+        !ensure_dyn_smem(reinterpret_cast<const void*>(gemm_w2_kernel<2, false>), GmCfg<2>::kSmem) ||
+        !ensure_dyn_smem(reinterpret_cast<const void*>(gemm_w2_kernel<1, true>), GmCfg<1>::kSmem) ||
+        !ensure_dyn_smem(reinterpret_cast<const void*>(gemm_w2_kernel<2, true>), GmCfg<2>::kSmem))
         return check_launch("bdq_gemm_w2(attr)");
     dim3 grid((unsigned)((OC + kGmN - 1) / kGmN), (unsigned)((M + kGmM * MT - 1) / (kGmM * MT)));
-    if (MT == 2)
-        gemm_w2_kernel<2><<<grid, kGmThreads, GmCfg<2>::kSmem, st>>>(map, (const uint32_t*)qweight, (const __half*)scales,
-                                                                     (const uint32_t*)qzeros, (__half*)out, (int)M, (int)IC, (int)OC,
-                                                                     group, zw, (int)ldo, peers);
-    else
-        gemm_w2_kernel<1><<<grid, kGmThreads, GmCfg<1>::kSmem, st>>>(map, (const uint32_t*)qweight, (const __half*)scales,
-                                                                     (const uint32_t*)qzeros, (__half*)out, (int)M, (int)IC, (int)OC,
-                                                                     group, zw, (int)ldo, peers);
-    return check_launch("bdq_gemm_w2");
+#define BDQ_GM(MTT, BT)                                                                                                            \
+    gemm_w2_kernel<MTT, BT><<<grid, kGmThreads, GmCfg<MTT>::kSmem, st>>>(map, wmap, (const uint32_t*)qweight, (const __half*)scales, \
+                                                                          (const uint32_t*)qzeros, (__half*)out, (int)M, (int)IC,  \
+                                                                          (int)OC, group, zw, (int)ldo, peers)
+    if (w_f16) { if (MT == 2) BDQ_GM(2, true); else BDQ_GM(1, true); }
+    else { if (MT == 2) BDQ_GM(2, false); else BDQ_GM(1, false); }
+#undef BDQ_GM
+    return check_launch(w_f16 ? "bdq_gemm_f16" : "bdq_gemm_w2");
 }
 
 }  // namespace bdq
@@ -383,4 +407,18 @@ extern "C" int bdq_gemm_w2_tp(const void* x, const int32_t* qweight, const void*
     for (int i = 0; i < n_peer; ++i)
         if (!peer_out[i] || ((uintptr_t)peer_out[i] % 16)) { set_error("gemm_w2_tp: peer pointer %d null or misaligned", i); return BDQ_ERR_ALIGN; }
     return launch_gemm_w2(x, qweight, scales, qzeros, out, M, IC, OC_local, group, zw, (cudaStream_t)stream, ldo, n_peer, peer_out);
+}
+
+// Plain fp16 GEMM on the same tcgen05 kernel: out [M, OC] = x [M, IC] @ w [OC, IC]^T, fp32 accumulate, both operands by TMA.
+// This library's own dense GEMM for weight formats that are dequantised to fp16 first (WQLinearNF3's prefill: bdq_nf3_dequant
+// + this, no cuBLAS); the reference has no counterpart (its NF3 never leaves the fake-quantiser).
+extern "C" int bdq_gemm_f16(const void* x, const void* w, void* out, int64_t M, int64_t IC, int64_t OC, bdq_stream_t stream) {
+    if (M < 0 || IC <= 0 || OC <= 0) { set_error("gemm_f16: M=%lld IC=%lld OC=%lld", (long long)M, (long long)IC, (long long)OC); return BDQ_ERR_SHAPE; }
+    if (M == 0) return BDQ_OK;
+    if (!x || !w || !out) { set_error("null tensor pointer"); return BDQ_ERR_SHAPE; }
+    if (IC % 64 != 0 || OC % 32 != 0 || ((uintptr_t)x % 16) || ((uintptr_t)w % 16) || ((uintptr_t)out % 16) || M >= (1ll << 31) || IC >= (1 << 24)) {
+        set_error("gemm_f16: needs IC %% 64 == 0, OC %% 32 == 0 and 16-byte aligned tensors");
+        return BDQ_ERR_UNSUPPORTED;
+    }
+    return launch_gemm_w2(x, nullptr, nullptr, nullptr, out, M, IC, OC, 128, 0, (cudaStream_t)stream, OC, 0, nullptr, w);
 }

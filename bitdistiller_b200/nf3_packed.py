@@ -66,6 +66,23 @@ def gemv_nf3(x, qweight, qhigh, scales, group_size=128):
     return out
 
 
+def gemm_f16(x, w):
+    """out [M, OC] = x [M, IC] @ w [OC, IC]^T on this library's tcgen05 GEMM (bdq_gemm_f16: both operands by TMA, fp32
+    accumulate, fp16 out)."""
+    L.require_cuda(x, w)
+    if x.dtype != torch.float16 or w.dtype != torch.float16:
+        raise TypeError("gemm_f16 expects float16 tensors")
+    x, w = x.contiguous(), w.contiguous()
+    M, ic = x.shape
+    oc = w.shape[0]
+    assert w.shape[1] == ic
+    out = torch.empty((M, oc), dtype=torch.float16, device=x.device)
+    with torch.cuda.device(x.device):
+        rc = L.lib().bdq_gemm_f16(L.ptr(x), L.ptr(w), L.ptr(out), L.i64(M), L.i64(ic), L.i64(oc), L.stream_ptr(x.device))
+    L.check(rc, "bdq_gemm_f16")
+    return out
+
+
 class WQLinearNF3(nn.Module):
     """NF3 counterpart of qmodule.WQLinear: buffers `qweight`, `qhigh`, `scales`, `bias` are the on-disk format."""
 
@@ -99,7 +116,14 @@ class WQLinearNF3(nn.Module):
         if x2.shape[0] <= 8:
             y = gemv_nf3(x2, self.qweight, self.qhigh, self.scales, self.group_size)
         else:
-            y = torch.matmul(x2, dequant_nf3(self.qweight, self.qhigh, self.scales, self.group_size).t())
+            # prefill: dequantise once (bdq_nf3_dequant, bit-equal to the NF3 fake-quantiser) and run this library's own tcgen05
+            # GEMM on it -- no cuBLAS on the path.  The 3-bit table decode costs ~3x the int2 digit trick per weight, too much to
+            # hide behind the MMAs inside the GEMM's producers; the dequantised copy costs 4 B/weight of HBM traffic per call.
+            w16 = dequant_nf3(self.qweight, self.qhigh, self.scales, self.group_size)
+            if self.in_features % 64 == 0 and self.out_features % 32 == 0:
+                y = gemm_f16(x2.half(), w16)
+            else:
+                raise L.BdqError("WQLinearNF3 prefill needs in_features % 64 == 0 and out_features % 32 == 0")
         if self.bias is not None:
             y = y + self.bias
         return y.reshape(out_shape)

@@ -264,6 +264,9 @@ int bdq_gptq_pack_w2(const uint8_t* codes, const uint8_t* zeros, int32_t* qweigh
  */
 int bdq_gemm_w2(const void* x, const int32_t* qweight, const void* scales, const int32_t* qzeros, void* out, int64_t M,
                 int64_t IC, int64_t OC, int group, bdq_stream_t stream);
+/* Plain fp16 GEMM on the same tcgen05 kernel (both operands by TMA): out [M, OC] = x [M, IC] @ w [OC, IC]^T, fp32 accumulate.
+ * IC % 64 == 0, OC % 32 == 0.  Used by WQLinearNF3's prefill after bdq_nf3_dequant (no cuBLAS on that path). */
+int bdq_gemm_f16(const void* x, const void* w, void* out, int64_t M, int64_t IC, int64_t OC, bdq_stream_t stream);
 
 /*
  * Tensor-parallel variants with the all-gather of the channel slices FUSED into the kernel epilogue (the

@@ -111,3 +111,22 @@ def test_second_device_in_one_process():
         outs.append((o.cpu(), v.cpu(), a.cpu(), b.cpu()))
     for p, q in zip(*outs):
         assert torch.equal(p, q)
+
+
+@pytest.mark.parametrize("m,oc,ic", [(128, 256, 64), (300, 1024, 4096), (2048, 4096, 4096), (77, 352, 1024), (257, 12288, 512), (9, 32, 128)])
+def test_gemm_f16_tcgen05_vs_fp32_matmul(m, oc, ic):
+    """bdq_gemm_f16: the same tcgen05 kernel with the B tile loaded by TMA from fp16 weights [OC, IC] (WQLinearNF3's prefill):
+    within rtol 1e-2 of the fp32 matmul of the same fp16 operands (partial last N tile, ragged M, both token-tile counts)."""
+    from bitdistiller_b200 import _lib as L
+    from bitdistiller_b200.nf3_packed import gemm_f16
+    g = torch.Generator().manual_seed(m + oc)
+    w = (torch.randn(oc, ic, generator=g) * 0.02).half().to(dev)
+    x = torch.randn(m, ic, generator=g).half().to(dev)
+    n0 = L.launch_count()
+    out = gemm_f16(x, w)
+    torch.cuda.synchronize()
+    assert L.launch_count() == n0 + 1 and out.shape == (m, oc) and out.dtype == torch.float16
+    ref = x.float() @ w.float().T
+    _check(out, ref, x, w)
+    with pytest.raises(L.BdqError):
+        gemm_f16(x[:, :ic - 8].contiguous(), w[:, :ic - 8].contiguous())
