@@ -62,14 +62,18 @@ def build(verbose=False):
                "-Xcompiler", "-fPIC"]
     bdir = os.path.join(OUT, "build")
     os.makedirs(bdir, exist_ok=True)
-    objs = []
-    for s in srcs:
+    objs, procs = [], []
+    for s in srcs:   # the three translation units compile in parallel (each spends minutes in the PyTorch headers)
         o = os.path.join(bdir, os.path.basename(s) + ".o")
         cmd = ["nvcc"] + nvflags + defs + inc + ["-c", s, "-o", o]
         if verbose:
             print(" ".join(cmd))
-        subprocess.check_call(cmd, stdout=subprocess.DEVNULL if not verbose else None)
+        procs.append((cmd, subprocess.Popen(cmd, stdout=subprocess.DEVNULL if not verbose else None,
+                                            stderr=subprocess.DEVNULL if not verbose else None)))
         objs.append(o)
+    for cmd, pr in procs:
+        if pr.wait() != 0:
+            raise subprocess.CalledProcessError(pr.returncode, cmd)
     cmd = ["nvcc", "-shared", "-o", so] + objs + [f"-L{tlib}", "-lc10", "-lc10_cuda", "-ltorch_cpu", "-ltorch_cuda",
                                                   "-ltorch", "-ltorch_python", f"-Xlinker=-rpath={tlib}"]
     subprocess.check_call(cmd)
