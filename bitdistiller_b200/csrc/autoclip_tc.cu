@@ -26,6 +26,7 @@
 #include "fq_int_elem.cuh"
 #include "fq_nf3_elem.cuh"
 #include "fakequant_thr.cuh"
+#include "fq_nf3_stair.cuh"
 
 namespace bdq {
 namespace actc {
@@ -39,13 +40,14 @@ constexpr int kThreads = 32 * (kWarpEpi0 + kNEpiWarps);   // 672
 constexpr int kXBytes = kTok * kG * 2;                    // 128 KB: [k half][512 tokens][128 B]
 constexpr int kABytes = 128 * kG * 2;                     // 32 KB:  [k half][128 rows][128 B]
 constexpr int kCandFloats = 12;
+constexpr int kCandP = 20;              // packed parameter words per slot (see the parameter role)
 
 struct Smem {   // offsets from the 1024-aligned base
     static constexpr int x = 0;
     static constexpr int a = x + kXBytes;                       // 2 buffers
     static constexpr int cand = a + 2 * kABytes;                // [2][kRowsUsed][12] floats
-    static constexpr int candp = cand + 2 * kRowsUsed * kCandFloats * 4;  // [2][kRowsUsed][8] u32: T pairs lo, hi, T1, T2, T3, -z, s + mode
-    static constexpr int wfp = candp + 2 * kRowsUsed * 8 * 4;           // [2][64] packed T pairs (the raw weight group)
+    static constexpr int candp = cand + 2 * kRowsUsed * kCandFloats * 4;  // [2][kRowsUsed][kCandP] u32: duplicated T pairs + mode word
+    static constexpr int wfp = candp + 2 * kRowsUsed * kCandP * 4;      // [2][64] packed T pairs (the raw weight group)
     static constexpr int ext = wfp + 2 * 256;                   // [kOT][2] floats: group max / min per channel
     static constexpr int errh = ext + kOT * 8;                  // [2 parity][2 halves][128] floats
     static constexpr int owb = errh + 2 * 2 * 128 * 4;          // [kNEpiWarps][2][32] floats
@@ -58,6 +60,8 @@ struct Smem {   // offsets from the 1024-aligned base
 // barrier indices
 constexpr int kBarX = 0, kBarAFull = 1, kBarAEmpty = 3, kBarAccFull = 5, kBarAccEmpty = 7, kBarPFull = 9, kBarPEmpty = 11;
 
+static_assert(Smem::total <= 227 * 1024, "autoclip_tc shared memory");
+
 struct Args {
     const void* w;
     void* best_max;
@@ -66,6 +70,7 @@ struct Args {
     float* best_err;
     int64_t co, ci, n_tok;
     int bits, quant_type, n_grid, nc, sem;
+    Nf3Stair stair;    // NF3 candidates in threshold form
     long long* prof;   // dev tool (BDQ_AUTOCLIP_TC_PROF): cycles every role of CTA (0, 0) spent waiting, see tools/prof_autoclip_roles.py
     Nf3Tables tb;
 };
@@ -268,17 +273,40 @@ __global__ void __launch_bounds__(kThreads, 1) autoclip_tc_kernel(const __grid_c
                     } else {
                         const Nf3Q p = nf3_group_params(cmx, cmn);
                         cp[0] = p.sp; cp[1] = p.sn; cp[2] = p.yp; cp[3] = p.yn; cp[6] = p.nan_group ? 1.f : 0.f;
+                        // NF3 in threshold form (fakequant_nf3_thr.cu): the candidate's seven verified x-space thresholds and
+                        // eight output values rT(level * scale); a candidate that fails the check is generated op by op
+                        using P = P2<DT>;
+                        float T[7];
+                        const bool ok = nf3_thresholds_1t<DT>(a.stair, p.sp, p.sn, T) && !p.nan_group;
+                        cp[11] = ok ? 2.f : 0.f;
+                        uint32_t* dp = candp + (pb * kRowsUsed + pt) * kCandP;
+#pragma unroll
+                        for (int k = 0; k < 5; ++k) dp[2 + k] = P::bits(P::dup(T[k]));
+                        dp[8] = P::bits(P::dup(T[5]));
+                        dp[9] = P::bits(P::dup(T[6]));
+                        const typename P::h2 s2p = P::dup(p.sp), s2n = P::dup(p.sn);
+#pragma unroll
+                        for (int c = 0; c < 8; ++c)
+                            dp[10 + c] = (c == 3) ? 0u : P::bits(__hmul2(P::from_bits(a.stair.lvl2[c]), c < 3 ? s2n : s2p));
                     }
                 }
             }
-            if (pt < kRowsUsed) {   // the same parameters as duplicated T pairs + a mode word: the row generators read two LDS.128
+            if (pt < kRowsUsed) {   // the same parameters as duplicated T pairs + a mode word: the row generators read LDS.128s
                 using P = P2<DT>;
                 const float* cp = cand + (pb * kRowsUsed + pt) * kCandFloats;
-                // mode: 0 threshold form, 1 pass-through (weight row), 2 unused slot, 3 op by op
-                const uint32_t mode = cp[7] == 1.f ? 1u : (cp[7] == 2.f ? 2u : (cp[11] != 0.f ? 0u : 3u));
-                uint4* dp = reinterpret_cast<uint4*>(candp + (pb * kRowsUsed + pt) * 8);
-                dp[0] = make_uint4(P::bits(P::dup(cp[4])), P::bits(P::dup(cp[5])), P::bits(P::dup(cp[8])), P::bits(P::dup(cp[9])));
-                dp[1] = make_uint4(P::bits(P::dup(cp[10])), P::bits(P::dup(-cp[2])), P::bits(P::dup(cp[0])), mode);
+                // mode: 0 int threshold form, 1 pass-through (weight row), 2 unused slot, 3 op by op, 4 NF3 threshold form
+                const uint32_t mode = cp[7] == 1.f ? 1u : (cp[7] == 2.f ? 2u : (cp[11] == 1.f ? 0u : (cp[11] == 2.f ? 4u : 3u)));
+                uint32_t* dp = candp + (pb * kRowsUsed + pt) * kCandP;
+                dp[0] = P::bits(P::dup(cp[4]));
+                dp[1] = P::bits(P::dup(cp[5]));
+                dp[7] = mode;
+                if (mode != 4u) {
+                    dp[2] = P::bits(P::dup(cp[8]));
+                    dp[3] = P::bits(P::dup(cp[9]));
+                    dp[4] = P::bits(P::dup(cp[10]));
+                    dp[5] = P::bits(P::dup(-cp[2]));
+                    dp[6] = P::bits(P::dup(cp[0]));
+                }
             }
             mbar_arrive(&bars[kBarPFull + pb]);
             bar_sync(1, kNParamWarps * 32);   // wred is rewritten by the next channel
@@ -298,8 +326,8 @@ __global__ void __launch_bounds__(kThreads, 1) autoclip_tc_kernel(const __grid_c
             const uint32_t wp[4] = {wraw.x, wraw.y, wraw.z, wraw.w};
             uint8_t* abase = As + ab * kABytes + kh * (kABytes / 2);
             for (int slot = rt >> 4; slot < kRowsUsed; slot += (kNRowWarps * 32) / 16) {
-                const uint4 pa = *reinterpret_cast<const uint4*>(candp + (pb * kRowsUsed + slot) * 8);
-                const uint4 pq = *reinterpret_cast<const uint4*>(candp + (pb * kRowsUsed + slot) * 8 + 4);
+                const uint4 pa = *reinterpret_cast<const uint4*>(candp + (pb * kRowsUsed + slot) * kCandP);
+                const uint4 pq = *reinterpret_cast<const uint4*>(candp + (pb * kRowsUsed + slot) * kCandP + 4);
                 const uint32_t mode = pq.w;
                 if (mode == 2u) continue;
                 const int row = row_of_slot(slot);
@@ -312,6 +340,24 @@ __global__ void __launch_bounds__(kThreads, 1) autoclip_tc_kernel(const __grid_c
                         const h2 x2 = __hmin2(__hmax2(P::from_bits(wp[i]), lo2), hi2);
                         const h2 c2 = __hadd2(__hadd2(__hge2(x2, t1), __hge2(x2, t2)), __hge2(x2, t3));
                         o4[i] = P::bits(__hmul2(__hadd2(c2, nz2), s2));   // rT((c - z) * s)
+                    }
+                } else if (mode == 4u) {   // NF3 threshold form: clamp, 7 packed compares + 7 bit selects per pair
+                    const uint4 pr = *reinterpret_cast<const uint4*>(candp + (pb * kRowsUsed + slot) * kCandP + 8);    // T5, T6, v0, v1
+                    const uint4 pv = *reinterpret_cast<const uint4*>(candp + (pb * kRowsUsed + slot) * kCandP + 12);   // v2 .. v5
+                    const uint2 pw = *reinterpret_cast<const uint2*>(candp + (pb * kRowsUsed + slot) * kCandP + 16);   // v6, v7
+                    const h2 lo2 = P::from_bits(pa.x), hi2 = P::from_bits(pa.y);
+                    const uint32_t tk[7] = {pa.z, pa.w, pq.x, pq.y, pq.z, pr.x, pr.y};
+                    const uint32_t vk[8] = {pr.z, pr.w, pv.x, pv.y, pv.z, pv.w, pw.x, pw.y};
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const h2 x2 = __hmin2(__hmax2(P::from_bits(wp[i]), lo2), hi2);
+                        uint32_t o = vk[0];
+#pragma unroll
+                        for (int k = 0; k < 7; ++k) {
+                            const uint32_t m = __hge2_mask(x2, P::from_bits(tk[k]));
+                            asm("lop3.b32 %0, %1, %2, %3, 0xCA;" : "=r"(o) : "r"(m), "r"(vk[k + 1]), "r"(o));   // m ? v : o
+                        }
+                        o4[i] = o;
                     }
                 } else if (mode == 1u) {
 #pragma unroll
@@ -485,6 +531,7 @@ int launch_autoclip_tc(const void* w, const void* x, void* best_max, void* best_
     a.co = co; a.ci = ci; a.n_tok = n_tok;
     a.bits = bits; a.quant_type = quant_type; a.n_grid = n_grid; a.nc = nc; a.sem = sem;
     a.tb = make_tables(dtype, sem);
+    a.stair = make_stair(a.tb, dtype);
     a.prof = g_actc_prof;
     dim3 grid((unsigned)(ci / kG), (unsigned)((co + kOT - 1) / kOT));
     if (dtype == BDQ_BF16) {

@@ -75,6 +75,14 @@ __device__ __forceinline__ U8 ldg256(const void* p) {
                  : "l"(p));
     return v;
 }
+// coherent variant for kernels that rewrite the memory they read (in-place apply_clip): .nc promises read-only data
+__device__ __forceinline__ U8 ld256(const void* p) {
+    U8 v;
+    asm volatile("ld.global.L1::no_allocate.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(v.r[0]), "=r"(v.r[1]), "=r"(v.r[2]), "=r"(v.r[3]), "=r"(v.r[4]), "=r"(v.r[5]), "=r"(v.r[6]), "=r"(v.r[7])
+                 : "l"(p) : "memory");
+    return v;
+}
 __device__ __forceinline__ void stg256(void* p, const U8& v) {
     asm volatile("st.global.L1::no_allocate.v8.b32 [%8], {%0,%1,%2,%3,%4,%5,%6,%7};"
                  :: "r"(v.r[0]), "r"(v.r[1]), "r"(v.r[2]), "r"(v.r[3]), "r"(v.r[4]), "r"(v.r[5]), "r"(v.r[6]), "r"(v.r[7]), "l"(p)

@@ -101,8 +101,9 @@ def pseudo_quantize_tensor(w, n_bit=8, zero_point=True, q_group_size=-1, inplace
         raise UnboundLocalError("cannot access local variable 'min_val' where it is not associated with a value")
     _check_nan(w)
     src = w if w.is_contiguous() else w.contiguous()
-    out = src if (inplace and src is w) else None
-    dq, scales, zeros, _ = int_fakequant(src, n_bit, group, L.ROUND_HALF_EVEN, out=out, want_scale_zp=get_scale_zp)
+    # inplace: the kernels read w through ld.global.nc / __restrict__ (read-only contract), so they never write the buffer they
+    # read -- the result goes to a temporary and is copied back below (the reference's in-place ops allocate temporaries too)
+    dq, scales, zeros, _ = int_fakequant(src, n_bit, group, L.ROUND_HALF_EVEN, out=None, want_scale_zp=get_scale_zp)
     if inplace and dq is not w:
         w.copy_(dq.reshape(org_w_shape))
         dq = w
