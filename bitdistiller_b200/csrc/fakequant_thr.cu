@@ -213,7 +213,27 @@ __global__ void __launch_bounds__(kThrThreads, 4) int_thr_bwd_kernel(const uint8
         const IntQ p = int_group_params<DT>(mx, mn, qmax, sem);
         const bool safe = fmaxf(fabsf(mx), fabsf(mn)) * p.y < 1e30f;
         h2 t2[NT + 2];   // T_0 (mask low), T_1..T_NT (codes), T_{NT+1} (mask high)
-        const bool fast = group_thresholds<DT, RM, LPG, NT + 2>(p, -p.z, 0, safe, lane, t2);
+        bool fast = group_thresholds<DT, RM, LPG, NT>(p, -p.z, 1, safe, lane, t2 + 1);
+        {
+            // The two clamp-mask thresholds are almost never needed: the group minimum normally quantises to code 0 and the
+            // maximum to code NT, so the predicate (monotone in x) at the two extremes already says "no element is clamped"
+            // and the mask is all ones (T_0 = -inf, T_{NT+1} = +inf).  Only otherwise are the two thresholds searched.
+            float tlo = -INFINITY, thi = INFINITY;
+            const bool need_lo = !thr_pred<DT, RM>(mn, p, -p.z);
+            const bool need_hi = thr_pred<DT, RM>(mx, p, -p.z + (float)(NT + 1));
+            if (need_lo) {
+                bool o;
+                tlo = find_threshold<DT, RM>(-p.z, p, o);
+                fast = fast && o;
+            }
+            if (need_hi) {
+                bool o;
+                thi = find_threshold<DT, RM>(-p.z + (float)(NT + 1), p, o);
+                fast = fast && o;
+            }
+            t2[0] = P::dup(tlo);
+            t2[NT + 1] = P::dup(thi);
+        }
         float Gs = 0.f;
         int cnt = 0;   // low 16 bits: #(x == max), high 16 bits: #(x == min)
         if (fast) {
