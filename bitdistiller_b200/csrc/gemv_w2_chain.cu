@@ -19,6 +19,7 @@
 // removed.  Every byte crosses HBM exactly once per token.
 #include <cuda.h>
 #include <cstring>
+#include <mutex>
 
 #include "bdq_common.cuh"
 
@@ -559,4 +560,153 @@ extern "C" int bdq_gemv_w2_chain_run(const void* workspace, int n_phases, int64_
     unsigned long long* prof = (g_chain_prof && g_chain_prof_cap >= (int64_t)sm_count() * 2 * n_phases * 8) ? g_chain_prof : nullptr;
     cudaLaunchKernelEx(&cfg, chain::gemv_w2_chain_kernel, plan, n_phases, wpw, counters, lookahead, prof, dbg);
     return check_launch("bdq_gemv_w2_chain_run");
+}
+
+// ------------------------------------------------------------------------------------------------------------------------
+// bdq_gemv_w2_chain_static: the same persistent kernel for callers that cannot allocate device memory (no counterpart in
+// the reference -- include/bdq.h).  The kernel's scratch -- the barrier
+// counters and the device-side plan, which bdq_gemv_w2_chain_prepare / _run keep in a caller-provided workspace -- lives in
+// a file-scope __device__ array of BDQ_GEMV_CHAIN_STATIC_MAX_PHASES phases (16.5 KB, held by every GPU that loads the
+// library until exit).  No cudaMalloc / cudaFree / host allocation anywhere on this path: the plan is built in a stack
+// array, copied with cudaMemcpyAsync and the counters are cleared with cudaMemsetAsync on the caller's stream.
+// All calls on a device share the one array: two calls that overlap on the GPU (different streams) race on it.
+// The existing entry points above are untouched; the phase validation below repeats theirs on purpose.
+namespace bdq {
+namespace chain {
+
+constexpr int kStaticMaxPhases = BDQ_GEMV_CHAIN_STATIC_MAX_PHASES;
+constexpr int kStaticCounterBytes = 512;   // (kStaticMaxPhases + 1) u32 counters, padded so that the plan stays 256-aligned
+constexpr int kStaticBytes = kStaticCounterBytes + kStaticMaxPhases * (int)sizeof(Phase);
+static_assert((kStaticMaxPhases + 1) * 4 <= kStaticCounterBytes, "counter block");
+
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticBytes];
+
+constexpr int kMaxDevices = 64;
+static std::mutex g_static_mu;
+static unsigned char* g_static_ptr[kMaxDevices];   // device address of g_static_scratch on device i (the host-side name is NOT one)
+
+// once per device, with that device current
+static unsigned char* static_scratch_ptr() {
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) {
+        set_error("gemv_w2_chain_static: cudaGetDevice failed / device index beyond %d", kMaxDevices - 1);
+        return nullptr;
+    }
+    std::lock_guard<std::mutex> lk(g_static_mu);
+    if (!g_static_ptr[dev]) {
+        unsigned char* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress((void**)&p, g_static_scratch);
+        if (e != cudaSuccess || !p) {
+            set_error("gemv_w2_chain_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+            (void)cudaGetLastError();
+            return nullptr;
+        }
+        g_static_ptr[dev] = p;
+    }
+    return g_static_ptr[dev];
+}
+
+// one bdq_gemv_phase_t -> one device-side Phase (same rules as bdq_gemv_w2_chain_prepare)
+static int fill_phase_static(const bdq_gemv_phase_t& s, int p, int grid, Phase& d) {
+    memset(&d, 0, sizeof(d));
+    const int64_t IC = s.IC;
+    const bool silu = (s.flags & BDQ_GEMV_SILU_MUL) != 0;
+    if (s.nmat < 1 || s.nmat > kMaxMats || !s.x || IC <= 0 || IC % 128 != 0 || IC > (1 << 20) || ((uintptr_t)s.x % 16) || s.group != 128 ||
+        (silu && (s.nmat != 2 || s.OC[0] != s.OC[1]))) {
+        set_error("gemv_w2_chain_static: phase %d: need 1..4 matrices, group 128, IC %% 128 == 0, 16-byte aligned x", p);
+        return BDQ_ERR_UNSUPPORTED;
+    }
+    const int zw = bdq_zeros_width(IC, 128, 2);
+    int total_rb = 0;
+    for (int i = 0; i < kMaxMats; ++i) {
+        const int k = i < s.nmat ? i : s.nmat - 1;
+        if (i < s.nmat) {
+            if (s.OC[i] <= 0 || s.OC[i] % 16 != 0 || !s.qweight[i] || !s.scales[i] || !s.qzeros[i] || (!s.out[i] && !(silu && i == 1)) ||
+                ((uintptr_t)s.qweight[i] % 32) || ((uintptr_t)s.scales[i] % 4) || ((uintptr_t)s.qzeros[i] % 4)) {
+                set_error("gemv_w2_chain_static: phase %d matrix %d: OC %% 16, non-null, 32-byte aligned qweight required", p, i);
+                return BDQ_ERR_UNSUPPORTED;
+            }
+            total_rb += (int)(s.OC[i] / 16);
+            d.qw_bytes[i] = (unsigned int)(s.OC[i] * (IC / 4));
+            d.sc_bytes[i] = (unsigned int)(s.OC[i] * zw * 32);
+            d.qz_bytes[i] = (unsigned int)(s.OC[i] * zw * 4);
+        }
+        d.qw[i] = (const uint8_t*)s.qweight[k];
+        d.sc[i] = (const __half*)s.scales[k];
+        d.qz[i] = (const uint32_t*)s.qzeros[k];
+        d.out[i] = (__half*)s.out[k];
+        d.rb_end[i] = total_rb;
+    }
+    const int nwin = (int)((IC / 128 + 3) / 4);
+    d.x = (const __half*)s.x;
+    d.IC = (int)IC;
+    d.zw = zw;
+    d.wpw = (nwin + kWarps - 1) / kWarps;
+    d.silu = silu ? 1 : 0;
+    const int units = silu ? total_rb / 2 : total_rb;
+    d.rb_q = units / grid;
+    d.rb_r = units % grid;
+    d.nmat = s.nmat;
+    d.wait = (s.flags & BDQ_GEMV_CHAIN_NOWAIT) ? 0 : 1;
+    return BDQ_OK;
+}
+
+}  // namespace chain
+}  // namespace bdq
+
+extern "C" int bdq_gemv_w2_chain_static(const bdq_gemv_phase_t* phases, int n_phases, int lookahead, bdq_stream_t stream) {
+    if (!phases || n_phases < 1) { set_error("gemv_w2_chain_static: null arguments / no phases"); return BDQ_ERR_SHAPE; }
+    if (n_phases > chain::kStaticMaxPhases) {
+        set_error("gemv_w2_chain_static: %d phases exceed the static scratch (BDQ_GEMV_CHAIN_STATIC_MAX_PHASES = %d): split the chain "
+                  "or use bdq_gemv_w2_chain_prepare / _run with a caller-provided workspace", n_phases, chain::kStaticMaxPhases);
+        return BDQ_ERR_SHAPE;
+    }
+    const int grid = sm_count() * 2;
+    chain::Phase host[chain::kStaticMaxPhases];   // 16 KB of stack: no host allocation either
+    int wpw = 1;
+    for (int p = 0; p < n_phases; ++p) {
+        const int rc = chain::fill_phase_static(phases[p], p, grid, host[p]);
+        if (rc != BDQ_OK) return rc;
+        wpw = host[p].wpw > wpw ? host[p].wpw : wpw;
+    }
+    const int smem = chain::smem_bytes(wpw, n_phases);
+    if (smem > 112 * 1024) {
+        set_error("gemv_w2_chain_static: %d phases with these in_features need %d B of shared memory (> 112 KB, two CTAs per SM): "
+                  "split the chain", n_phases, smem);
+        return BDQ_ERR_UNSUPPORTED;
+    }
+    unsigned char* scratch = chain::static_scratch_ptr();
+    if (!scratch) return BDQ_ERR_CUDA;
+    const void* kern = reinterpret_cast<const void*>(chain::gemv_w2_chain_kernel);
+    if (!ensure_dyn_smem(kern, 112 * 1024)) return check_launch("bdq_gemv_w2_chain_static(attr)");
+    int occ = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, chain::gemv_w2_chain_kernel, chain::kThreads, (size_t)smem) != cudaSuccess || occ < 2) {
+        set_error("gemv_w2_chain_static: the kernel needs two resident CTAs per SM (occupancy %d)", occ);
+        return BDQ_ERR_UNSUPPORTED;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    unsigned int* counters = reinterpret_cast<unsigned int*>(scratch);
+    const chain::Phase* plan = reinterpret_cast<const chain::Phase*>(scratch + chain::kStaticCounterBytes);
+    // the array keeps the previous call's contents: the counters must start at zero, the plan is overwritten.  `host` is
+    // pageable stack memory, so cudaMemcpyAsync has staged it when it returns (stream-ordered behind the previous call).
+    cudaError_t e = cudaMemsetAsync(counters, 0, chain::kStaticCounterBytes, st);
+    if (e == cudaSuccess)
+        e = cudaMemcpyAsync(scratch + chain::kStaticCounterBytes, host, (size_t)n_phases * sizeof(chain::Phase), cudaMemcpyHostToDevice, st);
+    if (e != cudaSuccess) {
+        set_error("gemv_w2_chain_static: staging the plan: %s", cudaGetErrorString(e));
+        (void)cudaGetLastError();
+        return BDQ_ERR_CUDA;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(chain::kThreads);
+    cfg.dynamicSmemBytes = (size_t)smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeCooperative;
+    at[0].val.cooperative = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    cudaLaunchKernelEx(&cfg, chain::gemv_w2_chain_kernel, plan, n_phases, wpw, counters, lookahead, (unsigned long long*)nullptr, 0);
+    return check_launch("bdq_gemv_w2_chain_static");
 }

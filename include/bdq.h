@@ -217,6 +217,23 @@ int bdq_gemv_w2_chain_run(const void* workspace, int n_phases, int64_t max_IC, i
 int bdq_gemv_w2_chain_set_prof(void* device_buf_u64, int64_t capacity_u64);   /* dev tool: per-phase %globaltimer marks */
 
 /*
+ * bdq_gemv_w2_chain_static: the decode chain for callers that cannot allocate device memory (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid cudaMalloc).  It has NO counterpart in the reference.
+ * Same kernel, same arithmetic and bit-equal outputs as _prepare + _run, but the
+ * kernel's scratch (barrier counters + device-side plan) lives in a file-scope `static __device__ __align__(256)` array
+ * inside the library (16.5 KB, held by every GPU that loads the library until exit) instead of a caller workspace.
+ * The call allocates nothing -- no cudaMalloc / cudaFree, no host malloc: it validates the phases into a stack array,
+ * clears the counters (cudaMemsetAsync), stages the plan (cudaMemcpyAsync) and launches, all on `stream`.
+ *   n_phases > BDQ_GEMV_CHAIN_STATIC_MAX_PHASES  -> BDQ_ERR_SHAPE with a message (split the chain or use _prepare / _run)
+ *   plan does not fit the kernel's shared memory -> BDQ_ERR_UNSUPPORTED (same limit as bdq_gemv_w2_chain_max_phases)
+ * Every call on a device shares the one array, which keeps the previous call's contents (the counters are cleared at
+ * every call): calls in one stream are ordered and safe, calls that OVERLAP on the GPU (different streams) race.
+ * The caller still passes all inputs and outputs (x, packed weights, out[]) inside `phases`.
+ */
+#define BDQ_GEMV_CHAIN_STATIC_MAX_PHASES 64
+int bdq_gemv_w2_chain_static(const bdq_gemv_phase_t* phases, int n_phases, int lookahead, bdq_stream_t stream);
+
+/*
  * Packed NF3 (3 bits per weight + two fp16 scales per group).  The reference has no packed NF3 format or kernel
  * (quantization/qmodule.py:77 accepts w_bit 2 and 4 only), so the layout is this library's own; its contract is that
  * bdq_nf3_dequant(pack(w)) equals SteN2F3Quantizer.forward(w) / pseudo_quantize_n2f3_tensor(w)
