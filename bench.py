@@ -725,6 +725,16 @@ def secondary_metrics(torch, dev, peak):
                                          "gbs": big["gbs"], "frac_of_hbm_peak": big["frac_of_hbm_peak"],
                                          "what": "the same batch-1 kernel on one lm_head-sized launch (cold, distinct copies)"}
     try:
+        from tools import bench_nf3_gemv
+        r = bench_nf3_gemv.run(dev, peak, shapes=[(151936, 4096)])[0]
+        out["gemv_nf3_kernel_streaming"] = {"shape": r["shape"], "mb": r["mb"], "us_per_launch": r["us"], "gbs": r["gbs"],
+                                            "frac_of_hbm_peak": r["frac_of_hbm_peak"], "bytes_per_weight": 0.40625,
+                                            "what": "packed NF3 (3 bits + two fp16 scales per group of 128) batch-1 GEMV on one lm_head-sized "
+                                                    "launch, L2-cold distinct copies, CUDA graph: PRMT level lookup + INT8 mma.sync "
+                                                    "(gemv_nf3_stream.cu); the reference has no packed NF3 kernel"}
+    except Exception as e:
+        out["gemv_nf3_kernel_streaming"] = {"error": f"{type(e).__name__}: {e}"[:300]}
+    try:
         # the reference's own kernels on this GPU (baseline/_ref, shipped by baseline/build_ref.py): the perf bars of SURVEY 8d 5a/5b
         from tools import bench_vs_reference
         pk = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}

@@ -1,42 +1,15 @@
-// Packed NF3 (3 bits per weight + two fp16 scales per group): pack, dequantise, decode GEMV.
-//
-// The reference has NO packed NF3 format or kernel (WQLinear takes w_bit 2 and 4 only), so
-// the byte layout below is this build's own and its parity is pinned on VALUES: dequantising the packed tensors must
-// reproduce SteN2F3Quantizer.forward / pseudo_quantize_n2f3_tensor (quantization/quantizer.py:113-116,184-242) bit for
-// bit in fp16.
-//
-// Format for a [OC, IC] weight, group G (IC % 32 == 0, G % 32 == 0):
-//   level index e in 0..7 = position in the ascending staircase -1, neg_lvl[2], neg_lvl[1], 0, pos_lvl[1..4]
-//     (e < 3: negative level, scaled by sn = |group min|;  e >= 3: zero or positive level, scaled by sp = |group max|)
-//   qweight int32 [OC, IC/16]: bits [2i, 2i+2) of word c = low two bits of e of input channel 16c + i (the int2 layout)
-//   qhigh   int32 [OC, IC/32]: bit 16w + i of word c = high bit of e of input channel 32c + 16w + i
-//   scales  fp16  [OC, 2*IC/G]: (sp, sn) per group
-// 0.375 B + 4/G B per weight = 0.40625 B/weight at G = 128.
-//
-// This is the first version of the path: the GEMV decodes through a per-lane shared-memory table on the CUDA cores
-// (correct, about a fifth of the HBM roofline); the digit-plane trick of the int2 kernel does not carry over because
-// the NF3 levels are not an affine function of the code.
+// Packed NF3 (3 bits per weight + two fp16 scales per group): pack, dequantise, small-shape decode GEMV.
+// Format and its rationale: nf3_packed.cuh (0.375 B + 4/G B per weight = 0.40625 B/weight at G = 128).
+// The bandwidth-bound decode GEMV (group 128, OC % 16 == 0) is gemv_nf3_stream.cu; the pair-lookup kernel below serves every
+// other shape.
 #include <cuda_fp16.h>
 
 #include <algorithm>
 #include <cstdlib>
 
-#include "bdq_common.cuh"
-#include "fq_nf3_elem.cuh"
+#include "nf3_packed.cuh"
 
 namespace bdq {
-
-struct Nf3Levels {
-    float lvl[8];   // ascending staircase, rounded to fp16
-};
-
-static Nf3Levels nf3_levels_f16() {
-    const Nf3Tables t = make_tables(kF16, 0);
-    Nf3Levels l;
-    l.lvl[0] = t.neg_lvl[3]; l.lvl[1] = t.neg_lvl[2]; l.lvl[2] = t.neg_lvl[1]; l.lvl[3] = 0.f;
-    for (int i = 1; i < 5; ++i) l.lvl[3 + i] = t.pos_lvl[i];
-    return l;
-}
 
 // codes as written by bdq_nf3_fakequant_fwd (fq_nf3_elem.cuh: 0 = zero, 1..4 = pos_lvl[1..4], 5..7 = neg_lvl[1..3]) -> e
 __device__ __forceinline__ uint32_t nf3_code_to_e(uint32_t c) { return c == 0u ? 3u : (c <= 4u ? c + 3u : 7u - c); }
@@ -54,7 +27,7 @@ __global__ void __launch_bounds__(256) nf3_pack_kernel(const uint8_t* __restrict
             const uint32_t code = (in[i >> 2] >> (8 * (i & 3))) & 0xffu;
             const uint32_t e = code > 7u ? 3u : nf3_code_to_e(code);   // 255 (NaN group) packs as zero
             lo[i >> 4] |= (e & 3u) << (2 * (i & 15));
-            hi |= (e >> 2) << i;
+            hi |= (e >> 2) << nf3_hbit_pos(i);
         }
         qweight[2 * c] = lo[0];
         qweight[2 * c + 1] = lo[1];
@@ -81,7 +54,7 @@ __global__ void __launch_bounds__(256) nf3_dequant_kernel(const uint32_t* __rest
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
                 const int k = i + h;
-                const uint32_t e = ((lo[k >> 4] >> (2 * (k & 15))) & 3u) | (((hi >> k) & 1u) << 2);
+                const uint32_t e = ((lo[k >> 4] >> (2 * (k & 15))) & 3u) | (((hi >> nf3_hbit_pos(k)) & 1u) << 2);
                 v[h] = lv.lvl[e] * (e < 3u ? sn : sp);   // exact product of two fp16 values; rounded once below
             }
             const __half2 p = __floats2half2_rn(v[0], v[1]);
@@ -93,54 +66,9 @@ __global__ void __launch_bounds__(256) nf3_dequant_kernel(const uint32_t* __rest
     }
 }
 
-// Decode GEMV, first version: one warp per output channel, lanes stride over 32-channel chunks; levels come from a
-// per-lane copy of the 8-entry table in shared memory (bank = lane: conflict free).
 constexpr int kNgThreads = 256;
-__global__ void __launch_bounds__(kNgThreads) nf3_gemv_kernel(const __half* __restrict__ x, const uint32_t* __restrict__ qweight,
-                                                              const uint32_t* __restrict__ qhigh, const __half* __restrict__ scales,
-                                                              __half* __restrict__ out, int B, int IC, int OC, int chunks_per_group,
-                                                              const Nf3Levels lv) {
-    __shared__ float2 lut[8][kNgThreads];   // (level if e >= 3 else 0, level if e < 3 else 0)
-    const int tid = threadIdx.x, lane = tid & 31;
-#pragma unroll
-    for (int e = 0; e < 8; ++e) lut[e][tid] = make_float2(e >= 3 ? lv.lvl[e] : 0.f, e < 3 ? lv.lvl[e] : 0.f);
-    __syncwarp();
-    const int cpr = IC >> 5, ngroups = cpr / chunks_per_group;
-    const int64_t warp = (int64_t)blockIdx.x * (kNgThreads / 32) + (tid >> 5);
-    const int64_t nwarps = (int64_t)gridDim.x * (kNgThreads / 32);
-    for (int64_t item = warp; item < (int64_t)OC * B; item += nwarps) {
-        const int row = (int)(item % OC), b = (int)(item / OC);
-        const __half* xb = x + (size_t)b * IC;
-        float acc = 0.f;
-        for (int c = lane; c < cpr; c += 32) {
-            const size_t wi = (size_t)row * cpr + c;
-            const uint32_t lo[2] = {__ldg(qweight + 2 * wi), __ldg(qweight + 2 * wi + 1)}, hi = __ldg(qhigh + wi);
-            const __half2 s2 = *reinterpret_cast<const __half2*>(scales + ((size_t)row * ngroups + c / chunks_per_group) * 2);
-            float ap = 0.f, an = 0.f;
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                const uint4 xv = __ldg(reinterpret_cast<const uint4*>(xb + c * 32) + q);
-                const uint32_t xr[4] = {xv.x, xv.y, xv.z, xv.w};
-#pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    const int k = q * 8 + i;
-                    const uint32_t e = ((lo[k >> 4] >> (2 * (k & 15))) & 3u) | (((hi >> k) & 1u) << 2);
-                    const float2 l = lut[e][tid];
-                    const __half2 xp = *reinterpret_cast<const __half2*>(&xr[i >> 1]);
-                    const float xf = (i & 1) ? __high2float(xp) : __low2float(xp);
-                    ap = fmaf(l.x, xf, ap);
-                    an = fmaf(l.y, xf, an);
-                }
-            }
-            acc = fmaf(__low2float(s2), ap, fmaf(__high2float(s2), an, acc));
-        }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-        if (lane == 0) out[(size_t)b * OC + row] = __float2half_rn(acc);
-    }
-}
 
-// Decode GEMV, second version (batch <= 8 rows of x handled one at a time): PAIR lookup.  Two adjacent weights are
+// Decode GEMV for the shapes the streaming kernel does not take (batch rows handled one at a time): PAIR lookup.  Two adjacent weights are
 // 4 bits of the low plane and 2 bits of the high plane: those 6 bits, masked in place at bits 8..13, ARE the byte offset of
 // a 64-entry table row (256 B = one 8-byte entry per lane, so a warp's lookup is conflict free whatever the codes are);
 // the entry holds the two levels as half2, once for the sp-scaled (zero / positive) side and once for the sn-scaled
@@ -220,9 +148,9 @@ __global__ void __launch_bounds__(kNgThreads) nf3_gemv2_kernel(const __half* __r
                 for (int w = 0; w < 2; ++w)
 #pragma unroll
                     for (int p = 0; p < 8; ++p) {
-                        const int k = 16 * w + 2 * p;
+                        const int hb = 4 * p + 2 * w;   // nf3_hbit_pos(16w + 2p): the pair's two high bits are adjacent
                         const uint32_t t1 = (4 * p <= 8) ? (low[w] << (8 - 4 * p)) : (low[w] >> (4 * p - 8));
-                        const uint32_t t2 = (k <= 12) ? (hi[r] << (12 - k)) : (hi[r] >> (k - 12));
+                        const uint32_t t2 = (hb <= 12) ? (hi[r] << (12 - hb)) : (hi[r] >> (hb - 12));
                         const uint32_t addr = (t2 & 0x3000u) | ((t1 & 0xF00u) | lanebase);
                         const uint2 l = lds64(addr);
                         const __half2 x2 = *reinterpret_cast<const __half2*>(&xr[8 * w + p]);
@@ -298,20 +226,15 @@ extern "C" int bdq_gemv_nf3(const void* x, const int32_t* qweight, const int32_t
         return BDQ_ERR_SHAPE;
     }
     if (((uintptr_t)x % 16) || ((uintptr_t)scales % 4)) { set_error("gemv_nf3: x must be 16-byte aligned"); return BDQ_ERR_ALIGN; }
-    static const bool v1 = getenv("BDQ_NF3_GEMV_V1") != nullptr;    // the first-version kernel, kept for A/B timing
-    if (!v1) {
-        const int64_t cpr2 = IC / 32, KB2 = (cpr2 + 31) / 32, slices2 = KB2 < 8 ? KB2 : 8, rbpc2 = 8 / slices2;
-        const int64_t nrb2 = (OC + kNg2Rows - 1) / kNg2Rows, items2 = ((nrb2 + rbpc2 - 1) / rbpc2) * B;
-        const int grid2 = (int)std::min<int64_t>(items2, (int64_t)sm_count() * 4);
-        nf3_gemv2_kernel<<<grid2, kNgThreads, 0, (cudaStream_t)stream>>>((const __half*)x, (const uint32_t*)qweight, (const uint32_t*)qhigh,
-                                                                         (const __half*)scales, (__half*)out, (int)B, (int)IC, (int)OC,
-                                                                         group / 32, nf3_levels_f16());
-        return check_launch("bdq_gemv_nf3");
+    {
+        const int rc = nf3_gemv_stream_launch(x, qweight, qhigh, scales, out, B, IC, OC, group, (cudaStream_t)stream);
+        if (rc != BDQ_ERR_UNSUPPORTED) return rc;
     }
-    const int64_t warps = OC * B;
-    const int grid = (int)std::min<int64_t>((warps + 7) / 8, (int64_t)sm_count() * 8);
-    nf3_gemv_kernel<<<grid, kNgThreads, 0, (cudaStream_t)stream>>>((const __half*)x, (const uint32_t*)qweight, (const uint32_t*)qhigh,
-                                                                   (const __half*)scales, (__half*)out, (int)B, (int)IC, (int)OC,
-                                                                   group / 32, nf3_levels_f16());
+    const int64_t cpr2 = IC / 32, KB2 = (cpr2 + 31) / 32, slices2 = KB2 < 8 ? KB2 : 8, rbpc2 = 8 / slices2;
+    const int64_t nrb2 = (OC + kNg2Rows - 1) / kNg2Rows, items2 = ((nrb2 + rbpc2 - 1) / rbpc2) * B;
+    const int grid2 = (int)std::min<int64_t>(items2, (int64_t)sm_count() * 4);
+    nf3_gemv2_kernel<<<grid2, kNgThreads, 0, (cudaStream_t)stream>>>((const __half*)x, (const uint32_t*)qweight, (const uint32_t*)qhigh,
+                                                                     (const __half*)scales, (__half*)out, (int)B, (int)IC, (int)OC,
+                                                                     group / 32, nf3_levels_f16());
     return check_launch("bdq_gemv_nf3");
 }

@@ -240,11 +240,15 @@ int bdq_gemv_w2_chain_static(const bdq_gemv_phase_t* phases, int n_phases, int l
  * (quantization/quantizer.py:113-116,184-242) bit for bit in fp16.
  *   level index e = position in the ascending staircase -1, -0.535, -0.247, 0, 0.183, 0.382, 0.623, 1
  *   qweight int32 [rows, cols/16]: bits [2i, 2i+2) of word c = low two bits of e of column 16c + i
- *   qhigh   int32 [rows, cols/32]: bit 16w + i of word c = high bit of e of column 32c + 16w + i
+ *   qhigh   int32 [rows, cols/32]: bit 4n + 2w + p of word c = high bit of e of column 32c + 16w + 2n + p (w, p in 0..1,
+ *           n in 0..7): ((qweight_word >> 2p) & 0x33333333) | ((qhigh_word << (2 - 2w - p)) & 0x44444444) is then eight
+ *           4-bit level indices = two PRMT selectors (the GEMV looks levels up with PRMT, no per-code extraction)
  *   scales  fp16  [rows, 2*cols/group]: (|group max|, |group min|) per group; e < 3 uses the second one
  * bdq_pack_nf3 takes the uint8 codes written by bdq_nf3_fakequant_fwd (cols % 32 == 0, 16-byte aligned).
- * bdq_gemv_nf3: out[b, oc] = fp16(sum_k x[b,k] * level * scale), x [B, IC] fp16, fp32 accumulation; first version
- * (CUDA-core table decode).  group % 32 == 0, IC % group == 0.
+ * bdq_gemv_nf3: out[b, oc] = fp16(sum_k x[b,k] * level * scale), x [B, IC] fp16.  group % 32 == 0, IC % group == 0.
+ * group 128 and OC % 16 == 0 (32-byte aligned qweight, 16-byte aligned qhigh) take the streaming kernel: PRMT level lookup
+ * into 16-bit fixed-point tables, INT8 tensor-pipe MMAs against block-fixed-point x (value error 2^-16 of the group's
+ * scale / largest activation, below the fp16 rounding of the dequantised weights); other shapes a CUDA-core pair lookup.
  */
 int bdq_pack_nf3(const uint8_t* codes, int32_t* qweight, int32_t* qhigh, int64_t rows, int64_t cols, bdq_stream_t stream);
 int bdq_nf3_dequant(const int32_t* qweight, const int32_t* qhigh, const void* scales, void* out_f16, int64_t rows, int64_t cols,

@@ -19,7 +19,9 @@ def _unpack_reference(qweight, qhigh):
     oc, ic = qw.shape[0], qw.shape[1] * 16
     k = np.arange(ic)
     lo = (qw[:, k // 16] >> (2 * (k % 16)).astype(np.uint32)) & 3
-    hi = (qh[:, k // 32] >> (k % 32).astype(np.uint32)) & 1
+    kk = k % 32   # nf3_packed.cuh: channel 16w + 2n + p of a 32-channel chunk keeps its high bit at 4n + 2w + p
+    pos = 4 * ((kk % 16) // 2) + 2 * (kk // 16) + (kk % 2)
+    hi = (qh[:, k // 32] >> pos.astype(np.uint32)) & 1
     return (lo | (hi << 2)).astype(np.int64)
 
 
@@ -100,3 +102,44 @@ def test_wqlinear_nf3_module():
     with pytest.raises(TypeError):
         from bitdistiller_b200.nf3_packed import pack_nf3
         pack_nf3(lin.weight.data.float(), 128)
+
+
+@pytest.mark.parametrize("oc,ic,kind", [(4096, 4096, "randn"), (512, 12288, "heavy"), (2048, 11008, "uniform"), (16, 512, "randn"),
+                                        (32000, 4096, "randn")])
+def test_gemv_nf3_stream_kernel(oc, ic, kind):
+    """The PRMT-lookup / INT8-MMA streaming kernel (group 128, OC % 16 == 0) on the decode shapes: skewed groups (sp != sn, both
+    signs of the level table and both scales in use), an outlier activation channel (block fixed point of x), against a
+    float64 matmul of the dequantised weights -- and against the pair-lookup kernel on the same tensors."""
+    from bitdistiller_b200 import nf3_packed as P
+    w = make_weight(kind, oc, ic, torch.float16, 11).float() * (ic ** -0.5 / 0.02)
+    w = (w + 0.4 * w.std() * (torch.arange(oc).view(-1, 1) % 3 - 1)).half().to(dev)      # rows skewed down / centred / up
+    qw, qh, sc = P.pack_nf3(w, 128)
+    dq = P.dequant_nf3(qw, qh, sc, 128)
+    x = torch.randn(1, ic, generator=torch.Generator().manual_seed(8)).half()
+    x[0, 7] = 40.0
+    x = x.to(dev)
+    y = P.gemv_nf3(x, qw, qh, sc, 128)
+    ref = x.double() @ dq.double().T
+    scale = x.double().abs() @ dq.double().abs().T
+    tol = 1e-2 * ref.abs() + 2e-3 * scale / np.sqrt(ic) + 1e-6
+    assert not bool(((y.double() - ref).abs() > tol).any())
+    assert float((y.double() - ref).norm() / ref.norm()) < 1e-3
+    # the other kernel (group 64 re-pack is not the same tensor, so force it by an OC that is not a multiple of 16)
+    y2 = P.gemv_nf3(x, qw[:oc - 8], qh[:oc - 8], sc[:oc - 8], 128)
+    assert float((y2.double() - y[:, :oc - 8].double()).norm() / ref.norm()) < 1e-3
+
+
+def test_gemv_nf3_stream_nonfinite():
+    from bitdistiller_b200 import nf3_packed as P
+    w = (make_weight("randn", 64, 1024, torch.float16, 3).float() * 1.5).half().to(dev)
+    qw, qh, sc = P.pack_nf3(w, 128)
+    x = torch.randn(1, 1024, generator=torch.Generator().manual_seed(1)).half().to(dev)
+    sc2 = sc.clone()
+    sc2[5, 6] = float("nan")                      # sp of group 3 of channel 5
+    y = P.gemv_nf3(x, qw, qh, sc2, 128)
+    assert bool(y[0, 5].isnan()) and int(y.isnan().sum()) == 1
+    x2 = x.clone()
+    x2[0, 300] = float("inf")
+    assert bool(P.gemv_nf3(x2, qw, qh, sc, 128).isnan().all())
+    z = torch.zeros_like(sc)                      # all-zero scales: zero output, not NaN
+    assert float(P.gemv_nf3(x, qw, qh, z, 128).abs().max()) == 0.0
