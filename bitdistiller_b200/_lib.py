@@ -80,6 +80,27 @@ def ptr(t):
     return ctypes.c_void_p(0 if t is None else t.data_ptr())
 
 
+class _Noop:
+    def __enter__(self):
+        return None
+
+    def __exit__(self, *exc):
+        return False
+
+
+_NOOP = _Noop()
+
+
+def on(device):
+    """`with L.on(t.device):` makes `device` current for a library call.  torch.cuda.device() costs several microseconds of
+    Python per call (prefill issues hundreds of 20-50 us GEMMs per forward), so when the device already is the current one
+    this is a no-op."""
+    idx = device.index if isinstance(device, torch.device) else device
+    if idx is None or idx == torch.cuda.current_device():
+        return _NOOP
+    return torch.cuda.device(device)
+
+
 def stream_ptr(device=None):
     return ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
 

@@ -44,7 +44,7 @@ def auto_2clip_layer(w, input_feat, n_bit, q_config, n_grid=20, max_shrink=0.5, 
     best_min = torch.empty((co, ng, 1), dtype=w.dtype, device=w.device)
     idx = torch.empty((co, ng), dtype=torch.int32, device=w.device) if return_info else None
     err = torch.empty((co, ng), dtype=torch.float32, device=w.device) if return_info else None
-    with torch.cuda.device(w.device):
+    with L.on(w.device):
         rc = L.lib().bdq_autoclip(L.ptr(wc), L.ptr(x), L.ptr(best_max), L.ptr(best_min), L.ptr(idx), L.ptr(err),
                                   L.i64(co), L.i64(ci), L.i64(n_tok), L.i64(row_stride), int(group_size), int(n_bit),
                                   L.QUANT_INT if quant_type == "int" else L.QUANT_NF3, int(n_grid),

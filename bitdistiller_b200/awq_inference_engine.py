@@ -30,7 +30,7 @@ def gemv_forward_cuda(in_feats, kernel, scaling_factors, zeros, w_bit, group_siz
     assert kernel.is_contiguous() and scaling_factors.is_contiguous() and zeros.is_contiguous()
     assert kernel.shape[1] * 16 == IC, "qweight must be [OC, IC/16] int32"
     out = torch.empty((B, OC), dtype=torch.float16, device=x.device)
-    with torch.cuda.device(x.device):
+    with L.on(x.device):
         rc = L.lib().bdq_gemv_w2(L.ptr(x), L.ptr(kernel), L.ptr(scaling_factors), L.ptr(zeros), L.ptr(out), L.i64(B),
                                  L.i64(IC), L.i64(OC), int(group_size), int(flags) | (GEMV_PDL if pdl else 0),
                                  L.stream_ptr(x.device))
@@ -61,7 +61,7 @@ def gemv_multi_forward_cuda(in_feats, kernels, scaling_factors, zeros, group_siz
     npf = len(prefetch)
     pf_ptr = (ctypes.c_void_p * max(npf, 1))(*[t.data_ptr() for t in prefetch])
     pf_len = (ctypes.c_int64 * max(npf, 1))(*[t.numel() * t.element_size() for t in prefetch])
-    with torch.cuda.device(x.device):
+    with L.on(x.device):
         rc = L.lib().bdq_gemv_w2_multi(L.ptr(x), n, arr(kernels), arr(scaling_factors), arr(zeros), arr(outs), oc,
                                        L.i64(IC), int(group_size), int(flags) | (GEMV_PDL if pdl else 0),
                                        npf, pf_ptr, pf_len, L.stream_ptr(x.device))
@@ -90,7 +90,7 @@ def gemv_silu_mul_forward_cuda(in_feats, gate, up, group_size, pdl=False, flags=
     arr = lambda a, b: (ctypes.c_void_p * 2)(a.data_ptr(), b.data_ptr())
     outs = (ctypes.c_void_p * 2)(out.data_ptr(), None)
     oc = (ctypes.c_int64 * 2)(OC, OC)
-    with torch.cuda.device(x.device):
+    with L.on(x.device):
         rc = L.lib().bdq_gemv_w2_multi(L.ptr(x), 2, arr(gate[0], up[0]), arr(gate[1], up[1]), arr(gate[2], up[2]), outs, oc,
                                        L.i64(IC), int(group_size), int(flags) | GEMV_SILU_MUL | (GEMV_PDL if pdl else 0),
                                        0, None, None, L.stream_ptr(x.device))
@@ -170,13 +170,13 @@ class DecodeChain:
             nbytes = int(lib.bdq_gemv_w2_chain_workspace_bytes(len(sub)))
             ws = torch.zeros(nbytes + 256, dtype=torch.uint8, device=dev)
             ptr = ctypes.c_void_p(ws.data_ptr() + (-ws.data_ptr()) % 256)
-            with torch.cuda.device(dev):
+            with L.on(dev):
                 rc = lib.bdq_gemv_w2_chain_prepare(arr, len(sub), ptr, L.i64(nbytes), L.stream_ptr(dev))
             L.check(rc, "bdq_gemv_w2_chain_prepare")
             self._runs.append((ws, ptr, len(sub)))
 
     def run(self, lookahead=0):
-        with torch.cuda.device(self.device):
+        with L.on(self.device):
             for _, ptr, n in self._runs:
                 rc = L.lib().bdq_gemv_w2_chain_run(ptr, n, L.i64(self.max_ic), int(lookahead), L.stream_ptr(self.device))
                 L.check(rc, "bdq_gemv_w2_chain_run")

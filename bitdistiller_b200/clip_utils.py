@@ -79,7 +79,7 @@ def clip_weight_(w, min_val, max_val):
     assert min_val.numel() == ng and w.numel() % ng == 0
     lo = min_val.to(w.dtype).contiguous()
     hi = max_val.to(w.dtype).contiguous()
-    with torch.cuda.device(w.device):
+    with L.on(w.device):
         rc = L.lib().bdq_apply_clip(L.ptr(w), L.ptr(lo), L.ptr(hi), L.i64(w.numel()), int(w.numel() // ng),
                                     L.dtype_code(w), L.stream_ptr(w.device))
     L.check(rc, "bdq_apply_clip")

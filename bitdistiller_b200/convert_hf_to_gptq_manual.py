@@ -50,7 +50,7 @@ def get_hf_quant_params(module, n_bit=2, zero_point=True, q_group_size=64):
     scales = torch.empty(ng, dtype=torch.float32, device=w.device)
     zeros = torch.empty(ng, dtype=torch.float32, device=w.device)
     codes = torch.empty(w.shape, dtype=torch.uint8, device=w.device)
-    with torch.cuda.device(w.device):
+    with L.on(w.device):
         rc = L.lib().bdq_int_fakequant_fwd(L.ptr(w), L.ptr(dq), L.ptr(scales), L.ptr(zeros), L.ptr(codes), L.ptr(None),
                                            L.ptr(None), L.i64(n), int(q_group_size), int(n_bit), L.F32,
                                            L.ROUND_HALF_EVEN, L.SEM_CPU, L.stream_ptr(w.device))
@@ -83,7 +83,7 @@ def convert_layer_to_gptq_format(hf_qweight_unpacked, hf_scales, hf_zero_points_
     zeros = _to_gpu(zp).to(torch.uint8).contiguous()
     qweight = torch.empty((ic // 16, oc), dtype=torch.int32, device=codes.device)
     qzeros = torch.empty((ic // group_size, oc // 16), dtype=torch.int32, device=codes.device)
-    with torch.cuda.device(codes.device):
+    with L.on(codes.device):
         rc = L.lib().bdq_gptq_pack_w2(L.ptr(codes), L.ptr(zeros), L.ptr(qweight), L.ptr(qzeros), L.i64(oc), L.i64(ic),
                                       int(group_size), int(bits), L.stream_ptr(codes.device))
     L.check(rc, "bdq_gptq_pack_w2")
@@ -113,7 +113,7 @@ def convert_linear_to_gptq(module, bits=2, group_size=64):
     qweight = torch.empty((ic // 16, oc), dtype=torch.int32, device=w.device)
     qzeros = torch.empty((ic // group_size, oc // 16), dtype=torch.int32, device=w.device)
     scales = torch.empty((ic // group_size, oc), dtype=torch.bfloat16, device=w.device)
-    with torch.cuda.device(w.device):
+    with L.on(w.device):
         rc = L.lib().bdq_gptq_export_w2(L.ptr(w), L.ptr(qweight), L.ptr(qzeros), L.ptr(scales), L.i64(oc), L.i64(ic),
                                         int(group_size), int(bits), L.dtype_code(w), L.stream_ptr(w.device))
     L.check(rc, "bdq_gptq_export_w2")

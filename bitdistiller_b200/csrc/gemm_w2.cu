@@ -5,7 +5,7 @@
 //   out[m, n] = fp16( sum_k x[m, k] * fp16( scales[n, k/G] * (code[n, k] - zero[n, k/G]) ) )      fp32 accumulate
 // (the dequantised weight is rounded to fp16 before the product exactly like the Triton kernel, triton_kernels.py:89-93).
 //
-// One CTA computes a 128 (tokens) x 256 (output channels) tile:
+// One CTA computes a (128 * MT tokens) x (NT output channels) tile, MT in {1, 2}, NT in {256, 128} (host-side choice):
 //   warp 0      : TMA producer -- x tiles [128 x 64] fp16, SWIZZLE_128B, cp.async.bulk.tensor + mbarrier complete_tx
 //   warp 1      : allocates 256 TMEM columns, then one elected lane issues tcgen05.mma (M128 N256 K16, kind::f16,
 //                 A and B from shared-memory descriptors, fp32 accumulator in TMEM) and tcgen05.commit
@@ -21,15 +21,17 @@
 
 namespace bdq {
 
-constexpr int kGmM = 128, kGmN = 256, kGmK = 64;     // CTA tile; kGmK fp16 = one 128-byte swizzle row
+constexpr int kGmM = 128, kGmK = 64;     // CTA tile: 128 tokens x NT (256 or 128) output channels; kGmK fp16 = one 128-byte swizzle row
 // MT = token tiles of 128 rows per CTA (1 or 2).  With MT = 2 the dequantised B stage feeds two accumulators (2 x 256 TMEM
 // columns = all of TMEM): the dequant work, which bounds the MT = 1 kernel, is amortised over twice the MMAs.
 constexpr int kGmABytes = kGmM * kGmK * 2;           // 16 KB per token tile
-constexpr int kGmBBytes = kGmN * kGmK * 2;           // 32 KB
 constexpr int kGmThreads = 32 * 10;
-template <int MT> struct GmCfg {
-    static constexpr int kStages = (MT == 1) ? 4 : 3;
-    static constexpr int kStageBytes = MT * kGmABytes + kGmBBytes;
+// NT = 128 serves grids that would leave most SMs idle with 256-wide tiles (k/v_proj: 64 -> 128 CTAs); the 256 producer
+// threads then split the k blocks (even / odd pairs) instead of the channels.
+template <int MT, int NT> struct GmCfg {
+    static constexpr int kBBytes = NT * kGmK * 2;        // 32 KB / 16 KB
+    static constexpr int kStageBytes = MT * kGmABytes + kBBytes;
+    static constexpr int kStages = (196 * 1024) / kStageBytes > 6 ? 6 : (196 * 1024) / kStageBytes;   // 4 / 3 (NT 256), 6 / 4 (NT 128)
     static constexpr int kSmem = kStages * kStageBytes + 1024 /*alignment slack*/ + 256 /*barriers*/;
 };
 
@@ -60,7 +62,7 @@ __device__ __forceinline__ uint64_t gm_desc(uint32_t smem_addr) {
     return (uint64_t)((smem_addr >> 4) & 0x3FFFu) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
 }
 // kind::f16 instruction descriptor: D fp32 (bit 4), A/B fp16 (0), both K-major, N >> 3 in [17,23), M >> 4 in [24,29)
-constexpr uint32_t kGmIdesc = (1u << 4) | ((uint32_t)(kGmN >> 3) << 17) | ((uint32_t)(kGmM >> 4) << 24);
+template <int NT> struct GmIdesc { static constexpr uint32_t v = (1u << 4) | ((uint32_t)(NT >> 3) << 17) | ((uint32_t)(kGmM >> 4) << 24); };
 
 __device__ __forceinline__ void gm_mma(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
     asm volatile(
@@ -119,7 +121,7 @@ struct GemmPeers {   // tensor parallel: this rank's column slice inside the pee
 // BTMA = true: plain fp16 GEMM out = x @ W^T with W [OC, IC] fp16 row-major (bdq_gemm_f16): the B tile is a second TMA load
 // (box 64 k x 256 channels, the same K-major SWIZZLE_128B layout the dequant producers write), the producer warps only
 // run the epilogue.  Used for weight formats whose in-register decode is too expensive to hide behind the MMAs (packed NF3).
-template <int MT, bool BTMA>
+template <int MT, bool BTMA, int NT>
 __global__ void __launch_bounds__(kGmThreads, 1) gemm_w2_kernel(const __grid_constant__ CUtensorMap xmap,
                                                                 const __grid_constant__ CUtensorMap wmap,
                                                                 const uint32_t* __restrict__ qweight,
@@ -127,7 +129,8 @@ __global__ void __launch_bounds__(kGmThreads, 1) gemm_w2_kernel(const __grid_con
                                                                 const uint32_t* __restrict__ qzeros, __half* __restrict__ out,
                                                                 int M, int IC, int OC, int G, int zw, int ldo,
                                                                 const GemmPeers peers) {
-    constexpr int kGmStages = GmCfg<MT>::kStages, kGmStageBytes = GmCfg<MT>::kStageBytes;
+    constexpr int kGmStages = GmCfg<MT, NT>::kStages, kGmStageBytes = GmCfg<MT, NT>::kStageBytes, kGmBBytes = GmCfg<MT, NT>::kBBytes;
+    constexpr int kGmN = NT;
     extern __shared__ uint8_t gm_smem_raw[];
     // align on the 32-bit shared address and ADD the offset, so that the pointer keeps its shared address space (STS / LDS
     // instead of generic ST / LD: the round trip through uintptr_t made all 280 stores of this kernel generic ones)
@@ -155,7 +158,7 @@ __global__ void __launch_bounds__(kGmThreads, 1) gemm_w2_kernel(const __grid_con
         if constexpr (BTMA) asm volatile("prefetch.tensormap [%0];" ::"l"(&wmap) : "memory");
     }
     if (warp == 1) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(gm_smem_u32(tmem_slot)), "r"(256 * MT) : "memory");
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(gm_smem_u32(tmem_slot)), "r"(NT * MT) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -193,7 +196,7 @@ __global__ void __launch_bounds__(kGmThreads, 1) gemm_w2_kernel(const __grid_con
                     const uint64_t adesc = gm_desc(a_addr + mt * kGmABytes);
 #pragma unroll
                     for (int k = 0; k < kGmK / 16; ++k)   // advance 32 bytes (>> 4 = 2) inside the swizzle row per K = 16
-                        gm_mma(tmem_d + mt * 256, adesc + 2 * k, bdesc + 2 * k, kGmIdesc, (kb | k) != 0 ? 1u : 0u);
+                        gm_mma(tmem_d + mt * NT, adesc + 2 * k, bdesc + 2 * k, GmIdesc<NT>::v, (kb | k) != 0 ? 1u : 0u);
                 }
                 gm_commit(&empty[s]);                 // frees the stage when these MMAs have read it
             }
@@ -201,7 +204,13 @@ __global__ void __launch_bounds__(kGmThreads, 1) gemm_w2_kernel(const __grid_con
         }
     } else {
         // ================= dequant producers: thread j <-> output channel n0 + j =================
-        const int j = tid - 64;
+        const int jt = tid - 64;
+        // NT = 256: thread jt owns channel jt and every k block.  NT = 128: channel jt % 128 and the pairs of k blocks gp with
+        // gp % 2 == jt / 128 (a 32-byte load is one pair), so the two halves of the producer warps fill different stages.
+        // (16 producer warps with one k block per 16-byte load were measured too: 10 % slower on every shape.)
+        const int j = (NT == 256) ? jt : (jt & 127);
+        constexpr int kPairStep = (NT == 256) ? 1 : 2;
+        const int gp0 = (NT == 256) ? 0 : (jt >> 7);
         if constexpr (!BTMA) {
         const int oc = min(n0 + j, OC - 1);   // a partial last tile re-reads the last channel; its columns are never stored
         const int wpr = IC >> 4;
@@ -211,23 +220,23 @@ __global__ void __launch_bounds__(kGmThreads, 1) gemm_w2_kernel(const __grid_con
         const int npair = nkb >> 1;   // 128 codes (two k blocks) per 32-byte load
         const int gshift = (G == 128) ? 1 : 0;   // k blocks per quantisation group: 2 (G = 128) or 1 (G = 64)
         // software prefetch one pair ahead: packed words, the pair's (up to) two scales and its zero-point word(s)
-        U8 cur = ldg256(wrow), nxt = cur;
+        U8 cur = ldg256(wrow + (gp0 < npair ? gp0 : 0) * 8), nxt = cur;
         __half csc[2], nsc[2];
         uint32_t czw[2], nzw[2];
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
-            const int grp = h >> gshift;
+            const int grp = ((gp0 < npair ? gp0 : 0) * 2 + h) >> gshift;
             csc[h] = srow[grp];
             czw[h] = __ldg(zrow + (grp >> 4));
             nsc[h] = csc[h];
             nzw[h] = czw[h];
         }
-        for (int gp = 0; gp < npair; ++gp) {
-            if (gp + 1 < npair) {
-                nxt = ldg256(wrow + (gp + 1) * 8);
+        for (int gp = gp0; gp < npair; gp += kPairStep) {
+            if (gp + kPairStep < npair) {
+                nxt = ldg256(wrow + (gp + kPairStep) * 8);
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
-                    const int grp = ((gp + 1) * 2 + h) >> gshift;
+                    const int grp = ((gp + kPairStep) * 2 + h) >> gshift;
                     nsc[h] = srow[grp];
                     nzw[h] = __ldg(zrow + (grp >> 4));
                 }
@@ -256,19 +265,20 @@ __global__ void __launch_bounds__(kGmThreads, 1) gemm_w2_kernel(const __grid_con
             for (int h = 0; h < 2; ++h) { csc[h] = nsc[h]; czw[h] = nzw[h]; }
         }
         }   // !BTMA
-        (void)j;
+        (void)j; (void)gp0;
         // ================= epilogue: TMEM -> registers -> fp16 -> global =================
         gm_mbar_wait(tmem_full, 0);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const int lane_grp = warp & 3;               // this warp may only touch TMEM lanes [32*(warp%4), +32)
-        const int col_half = (warp - 2) >> 2;        // 0: columns 0..127, 1: columns 128..255
+        const int col_half = (warp - 2) >> 2;        // 0: columns 0 .. NT/2-1, 1: the other half
+        constexpr int kCb = NT / 64;                 // 32-column chunks per warp and token tile
 #pragma unroll 1
-        for (int cbi = 0; cbi < 4 * MT; ++cbi) {
-            const int mt = cbi >> 2, cb = cbi & 3;
+        for (int cbi = 0; cbi < kCb * MT; ++cbi) {
+            const int mt = cbi / kCb, cb = cbi % kCb;
             const int row = m0 + mt * kGmM + lane_grp * 32 + lane;   // token
-            const int col = col_half * 128 + cb * 32;
+            const int col = col_half * (NT / 2) + cb * 32;
             uint32_t r[32];
-            const uint32_t taddr = tmem_d + ((uint32_t)(lane_grp * 32) << 16) + (uint32_t)(mt * 256 + col);
+            const uint32_t taddr = tmem_d + ((uint32_t)(lane_grp * 32) << 16) + (uint32_t)(mt * NT + col);
             asm volatile(
                 "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
@@ -298,7 +308,7 @@ __global__ void __launch_bounds__(kGmThreads, 1) gemm_w2_kernel(const __grid_con
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
-    if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(256 * MT) : "memory");
+    if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(NT * MT) : "memory");
 }
 
 // cuTensorMapEncodeTiled through the runtime's driver entry point lookup (libbdq.so must load on machines without a driver)
@@ -329,9 +339,27 @@ int launch_gemm_w2(const void* x, const int32_t* qweight, const void* scales, co
     CUtensorMap map;
     const cuuint64_t dims[2] = {(cuuint64_t)IC, (cuuint64_t)M};          // innermost first
     const cuuint64_t strides[1] = {(cuuint64_t)IC * 2};                   // bytes, dims 1..rank-1
-    // two token tiles per CTA when there is a second one to fill and the grid still covers at least half of the SMs
-    const int64_t ctas2 = ((OC + kGmN - 1) / kGmN) * ((M + 2 * kGmM - 1) / (2 * kGmM));
-    const int MT = (M > kGmM && ctas2 * 2 >= sm_count()) ? 2 : 1;
+    // Tile choice: 128 * MT tokens x NT channels per CTA, by estimated efficiency = CTAs / (waves * SMs) x the tile's own
+    // efficiency, measured on full grids at M = 2048 (profiles/r02_gemm_tiles.txt): (2, 256) 1.0, (2, 128) 0.77, (1, 256) 0.68,
+    // (1, 128) 0.57 -- the smaller the tile, the more often x is re-read from L2 per MAC, which is what bounds them.
+    // Qwen3-8B at M = 2048: everything keeps (2, 256) except k/v_proj alone, 64 CTAs of (1, 256) -> 128 of (1, 128)
+    // (0.30 -> 0.51 of the sustained bf16 peak).  BDQ_GEMM_TILE=<MT><NT/128> (e.g. 21) forces one (dev).
+    int MT = 1, NT = 256;
+    {
+        static const int forced = getenv("BDQ_GEMM_TILE") ? atoi(getenv("BDQ_GEMM_TILE")) : 0;
+        const double tile_eff[2][2] = {{0.57, 0.68}, {0.77, 1.00}};   // [MT - 1][NT / 128 - 1]
+        double best = -1.0;
+        for (int mt = 2; mt >= 1; --mt)
+            for (int nt = 256; nt >= 128; nt -= 128) {
+                if (mt == 2 && M <= kGmM) continue;
+                const int64_t tn = (OC + nt - 1) / nt, tm = (M + mt * kGmM - 1) / (mt * kGmM);
+                const int64_t ctas = tn * tm, waves = (ctas + sm_count() - 1) / sm_count();
+                const double useful = (double)OC * (double)M / ((double)(tn * nt) * (double)(tm * mt * kGmM));   // padding of partial tiles
+                const double e = (double)ctas / (double)(waves * sm_count()) * tile_eff[mt - 1][nt / 128 - 1] * useful;
+                if (e > best * 1.02) { best = e; MT = mt; NT = nt; }   // ties go to the larger tile
+            }
+        if (forced == 11 || forced == 12 || forced == 21 || forced == 22) { MT = forced / 10; NT = 128 * (forced % 10); if (M <= kGmM) MT = 1; }
+    }
     const cuuint32_t box[2] = {(cuuint32_t)kGmK, (cuuint32_t)(kGmM * MT)};
     const cuuint32_t estr[2] = {1, 1};
     CUresult r = enc(&map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(x), dims, strides, box, estr,
@@ -343,23 +371,30 @@ int launch_gemm_w2(const void* x, const int32_t* qweight, const void* scales, co
     if (w_f16) {   // plain fp16 weights [OC, IC]: B tiles by TMA
         const cuuint64_t wd[2] = {(cuuint64_t)IC, (cuuint64_t)OC};
         const cuuint64_t ws[1] = {(cuuint64_t)IC * 2};
-        const cuuint32_t wb[2] = {(cuuint32_t)kGmK, (cuuint32_t)kGmN};
+        const cuuint32_t wb[2] = {(cuuint32_t)kGmK, (cuuint32_t)NT};
         r = enc(&wmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(w_f16), wd, ws, wb, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                 CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r != CUDA_SUCCESS) { set_error("gemm_f16: cuTensorMapEncodeTiled failed (%d)", (int)r); return BDQ_ERR_CUDA; }
     }
-    if (!ensure_dyn_smem(reinterpret_cast<const void*>(gemm_w2_kernel<1, false>), GmCfg<1>::kSmem) ||
-        !ensure_dyn_smem(reinterpret_cast<const void*>(gemm_w2_kernel<2, false>), GmCfg<2>::kSmem) ||
-        !ensure_dyn_smem(reinterpret_cast<const void*>(gemm_w2_kernel<1, true>), GmCfg<1>::kSmem) ||
-        !ensure_dyn_smem(reinterpret_cast<const void*>(gemm_w2_kernel<2, true>), GmCfg<2>::kSmem))
-        return check_launch("bdq_gemm_w2(attr)");
-    dim3 grid((unsigned)((OC + kGmN - 1) / kGmN), (unsigned)((M + kGmM * MT - 1) / (kGmM * MT)));
-#define BDQ_GM(MTT, BT)                                                                                                            \
-    gemm_w2_kernel<MTT, BT><<<grid, kGmThreads, GmCfg<MTT>::kSmem, st>>>(map, wmap, (const uint32_t*)qweight, (const __half*)scales, \
-                                                                          (const uint32_t*)qzeros, (__half*)out, (int)M, (int)IC,  \
-                                                                          (int)OC, group, zw, (int)ldo, peers)
-    if (w_f16) { if (MT == 2) BDQ_GM(2, true); else BDQ_GM(1, true); }
-    else { if (MT == 2) BDQ_GM(2, false); else BDQ_GM(1, false); }
+    dim3 grid((unsigned)((OC + NT - 1) / NT), (unsigned)((M + kGmM * MT - 1) / (kGmM * MT)));
+#define BDQ_GM(MTT, BT, NTT)                                                                                                         \
+    do {                                                                                                                              \
+        if (!ensure_dyn_smem(reinterpret_cast<const void*>(gemm_w2_kernel<MTT, BT, NTT>), GmCfg<MTT, NTT>::kSmem))                    \
+            return check_launch("bdq_gemm_w2(attr)");                                                                                 \
+        gemm_w2_kernel<MTT, BT, NTT><<<grid, kGmThreads, GmCfg<MTT, NTT>::kSmem, st>>>(                                               \
+            map, wmap, (const uint32_t*)qweight, (const __half*)scales, (const uint32_t*)qzeros, (__half*)out, (int)M, (int)IC,       \
+            (int)OC, group, zw, (int)ldo, peers);                                                                                     \
+    } while (0)
+#define BDQ_GM_B(BT)                                                      \
+    do {                                                                  \
+        if (MT == 2 && NT == 256) BDQ_GM(2, BT, 256);                     \
+        else if (MT == 1 && NT == 256) BDQ_GM(1, BT, 256);                \
+        else if (MT == 2) BDQ_GM(2, BT, 128);                             \
+        else BDQ_GM(1, BT, 128);                                          \
+    } while (0)
+    if (w_f16) BDQ_GM_B(true);
+    else BDQ_GM_B(false);
+#undef BDQ_GM_B
 #undef BDQ_GM
     return check_launch(w_f16 ? "bdq_gemm_f16" : "bdq_gemm_w2");
 }

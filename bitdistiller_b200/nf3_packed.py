@@ -29,7 +29,7 @@ def pack_nf3(w, group_size=128, clip_min=None, clip_max=None):
     scales = torch.stack([sp.view(oc, -1), sn.view(oc, -1)], dim=-1).reshape(oc, -1).contiguous()
     qweight = torch.empty((oc, ic // 16), dtype=torch.int32, device=w.device)
     qhigh = torch.empty((oc, ic // 32), dtype=torch.int32, device=w.device)
-    with torch.cuda.device(w.device):
+    with L.on(w.device):
         rc = L.lib().bdq_pack_nf3(L.ptr(codes), L.ptr(qweight), L.ptr(qhigh), L.i64(oc), L.i64(ic), L.stream_ptr(w.device))
     L.check(rc, "bdq_pack_nf3")
     return qweight, qhigh, scales
@@ -41,7 +41,7 @@ def dequant_nf3(qweight, qhigh, scales, group_size=128):
     L.require_cuda(qweight, qhigh, scales)
     oc, ic = qweight.shape[0], qweight.shape[1] * 16
     out = torch.empty((oc, ic), dtype=torch.float16, device=qweight.device)
-    with torch.cuda.device(qweight.device):
+    with L.on(qweight.device):
         rc = L.lib().bdq_nf3_dequant(L.ptr(qweight), L.ptr(qhigh), L.ptr(scales), L.ptr(out), L.i64(oc), L.i64(ic),
                                      int(group_size), L.stream_ptr(qweight.device))
     L.check(rc, "bdq_nf3_dequant")
@@ -59,7 +59,7 @@ def gemv_nf3(x, qweight, qhigh, scales, group_size=128):
     oc = qweight.shape[0]
     assert qweight.shape[1] * 16 == ic
     out = torch.empty((B, oc), dtype=torch.float16, device=x.device)
-    with torch.cuda.device(x.device):
+    with L.on(x.device):
         rc = L.lib().bdq_gemv_nf3(L.ptr(x), L.ptr(qweight), L.ptr(qhigh), L.ptr(scales), L.ptr(out), L.i64(B), L.i64(ic),
                                   L.i64(oc), int(group_size), L.stream_ptr(x.device))
     L.check(rc, "bdq_gemv_nf3")
@@ -77,7 +77,7 @@ def gemm_f16(x, w):
     oc = w.shape[0]
     assert w.shape[1] == ic
     out = torch.empty((M, oc), dtype=torch.float16, device=x.device)
-    with torch.cuda.device(x.device):
+    with L.on(x.device):
         rc = L.lib().bdq_gemm_f16(L.ptr(x), L.ptr(w), L.ptr(out), L.i64(M), L.i64(ic), L.i64(oc), L.stream_ptr(x.device))
     L.check(rc, "bdq_gemm_f16")
     return out

@@ -62,7 +62,7 @@ def pack_wq(w_dq, scales, zeros, w_bit, group_size):
     qweight = torch.empty((rows, cols // pack_num), dtype=torch.int32, device=dev)
     qzeros = torch.empty((rows, zw), dtype=torch.int32, device=dev)
     qscales = torch.empty((rows, zw * pack_num), dtype=torch.float16, device=dev)
-    with torch.cuda.device(dev):
+    with L.on(dev):
         rc = L.lib().bdq_pack_wq(L.ptr(w_dq), L.ptr(scales), L.ptr(zeros), L.ptr(qweight), L.ptr(qzeros), L.ptr(qscales),
                                  L.i64(rows), L.i64(cols), int(G), int(w_bit), L.dtype_code(w_dq), L.stream_ptr(dev))
     L.check(rc, "bdq_pack_wq")

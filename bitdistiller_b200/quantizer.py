@@ -46,7 +46,7 @@ def int_fakequant(w, n_bit, group, round_mode, out=None, want_scale_zp=False, wa
         clip_min = clip_min.to(w.dtype).contiguous()
         clip_max = clip_max.to(w.dtype).contiguous()
         assert clip_min.numel() == ng and clip_max.numel() == ng
-    with torch.cuda.device(w.device):
+    with L.on(w.device):
         rc = L.lib().bdq_int_fakequant_fwd(L.ptr(w), L.ptr(dq), L.ptr(scales), L.ptr(zeros), L.ptr(codes),
                                            L.ptr(clip_min), L.ptr(clip_max), L.i64(n), int(group), int(n_bit),
                                            L.dtype_code(w), int(round_mode), L.semantics(), L.stream_ptr(w.device))
@@ -68,7 +68,7 @@ def nf3_fakequant(w, group, want_codes=False, want_scales=False, clip_min=None, 
         clip_min = clip_min.to(w.dtype).contiguous()
         clip_max = clip_max.to(w.dtype).contiguous()
         assert clip_min.numel() == ng and clip_max.numel() == ng
-    with torch.cuda.device(w.device):
+    with L.on(w.device):
         rc = L.lib().bdq_nf3_fakequant_fwd(L.ptr(w), L.ptr(dq), L.ptr(sp), L.ptr(sn), L.ptr(codes), L.ptr(clip_min),
                                            L.ptr(clip_max), L.i64(n), int(group), L.dtype_code(w), L.semantics(),
                                            L.stream_ptr(w.device))
@@ -161,7 +161,7 @@ class _SteIntFn(Function):
         gy = gy.to(x.dtype).contiguous()
         L.require_cuda(gy)
         gw = torch.empty_like(x)
-        with torch.cuda.device(x.device):
+        with L.on(x.device):
             rc = L.lib().bdq_int_ste_bwd(L.ptr(x), L.ptr(gy), L.ptr(gw), L.i64(x.numel()), int(ctx.group), int(ctx.bits),
                                          L.dtype_code(x), L.semantics(), L.stream_ptr(x.device))
         L.check(rc, "bdq_int_ste_bwd")
@@ -183,7 +183,7 @@ class _SteNf3Fn(Function):
         gy = gy.to(x.dtype).contiguous()
         L.require_cuda(gy)
         gw = torch.empty_like(x)
-        with torch.cuda.device(x.device):
+        with L.on(x.device):
             rc = L.lib().bdq_nf3_ste_bwd(L.ptr(x), L.ptr(gy), L.ptr(gw), L.i64(x.numel()), int(ctx.group),
                                          L.dtype_code(x), L.semantics(), L.stream_ptr(x.device))
         L.check(rc, "bdq_nf3_ste_bwd")

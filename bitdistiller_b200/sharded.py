@@ -200,7 +200,7 @@ def tp_gemv_fused(x, shards, rows, flags=0):
     npeer = rows[0].world - 1
     outp = (ctypes.c_void_p * n)(*own)
     peerp = (ctypes.c_void_p * max(len(peers), 1))(*peers)
-    with torch.cuda.device(x.device):
+    with L.on(x.device):
         rc = L.lib().bdq_gemv_w2_tp(L.ptr(x), n, qw, sc, qz, outp, ocl, L.i64(ic), 128, int(flags), npeer, peerp,
                                     L.stream_ptr(x.device))
     L.check(rc, "bdq_gemv_w2_tp")
@@ -217,7 +217,7 @@ def tp_gemm_fused(x, shard, rows, group_size=128):
     ocl = qweight.shape[0]
     own, peers = rows.slice_ptrs(rows.rank * ocl)
     peerp = (ctypes.c_void_p * max(len(peers), 1))(*peers)
-    with torch.cuda.device(x.device):
+    with L.on(x.device):
         rc = L.lib().bdq_gemm_w2_tp(L.ptr(x), L.ptr(qweight), L.ptr(scales), L.ptr(qzeros), ctypes.c_void_p(own), L.i64(M),
                                     L.i64(ic), L.i64(ocl), int(group_size), L.i64(rows.OC), len(peers), peerp,
                                     L.stream_ptr(x.device))
@@ -307,7 +307,7 @@ class PeerBarrier:
             self.hdl.barrier(channel=0)
             return
         self.epoch += 1
-        with torch.cuda.device(self.device):
+        with L.on(self.device):
             rc = L.lib().bdq_peer_barrier((ctypes.c_void_p * self.world)(*self.ptrs), self.rank, self.world,
                                           ctypes.c_uint32(self.epoch & 0xffffffff), L.stream_ptr(self.device))
         L.check(rc, "bdq_peer_barrier")
@@ -359,7 +359,7 @@ class ShardGather:
         peers = [p for i, p in enumerate(self.ptrs) if i != self.rank] if self.symmetric else []
         pc = (ctypes.c_void_p * max(len(peers), 1))(*[p + coff for p in peers])
         ps = (ctypes.c_void_p * max(len(peers), 1))(*[p + self._sz_off + soff for p in peers])
-        with torch.cuda.device(self.device):
+        with L.on(self.device):
             rc = L.lib().bdq_int2_shard_encode(L.ptr(w), ctypes.c_void_p(base + coff), ctypes.c_void_p(base + self._sz_off + soff),
                                                L.i64(w.numel()), int(self.group_size), L.dtype_code(w), int(self.round_mode),
                                                L.semantics(), len(peers), pc, ps, L.stream_ptr(self.device))
@@ -368,7 +368,7 @@ class ShardGather:
     def _decode(self, codes, sz):
         from . import _lib as L
         dq = torch.empty((self.rows, self.cols), dtype=self.dtype, device=self.device)
-        with torch.cuda.device(self.device):
+        with L.on(self.device):
             rc = L.lib().bdq_int2_shard_decode(L.ptr(codes), L.ptr(sz), L.ptr(dq), L.i64(dq.numel()), int(self.group_size),
                                                L.dtype_code(dq), L.stream_ptr(self.device))
         L.check(rc, "bdq_int2_shard_decode")
@@ -394,7 +394,7 @@ class ShardGather:
         g = reduce_scatter_rows(g_full.to(self.dtype).contiguous(), self.layout, self.rank, self.pg, average)
         w = w_shard.detach().contiguous()
         gw = torch.empty_like(w)
-        with torch.cuda.device(w.device):
+        with L.on(w.device):
             rc = L.lib().bdq_int_ste_bwd(L.ptr(w), L.ptr(g), L.ptr(gw), L.i64(w.numel()), int(self.group_size), 2,
                                          L.dtype_code(w), L.semantics(), L.stream_ptr(w.device))
         L.check(rc, "bdq_int_ste_bwd")
@@ -463,7 +463,7 @@ class ShardGatherNF3:
         pc = (ctypes.c_void_p * max(len(peers), 1))(*[p + coff for p in peers])
         ps = (ctypes.c_void_p * max(len(peers), 1))(*[p + self.ncode + soff for p in peers])
         st = L.stream_ptr(self.device)
-        with torch.cuda.device(self.device):
+        with L.on(self.device):
             rc = L.lib().bdq_nf3_shard_encode(L.ptr(w), ctypes.c_void_p(base + coff), ctypes.c_void_p(base + self.ncode + soff),
                                               L.i64(w.numel()), int(self.group_size), L.dtype_code(w), L.semantics(), len(peers), pc, ps, st)
             L.check(rc, "bdq_nf3_shard_encode")
@@ -485,7 +485,7 @@ class ShardGatherNF3:
         g = reduce_scatter_rows(g_full.to(self.dtype).contiguous(), self.layout, self.rank, self.pg, average)
         w = w_shard.detach().contiguous()
         gw = torch.empty_like(w)
-        with torch.cuda.device(w.device):
+        with L.on(w.device):
             rc = L.lib().bdq_nf3_ste_bwd(L.ptr(w), L.ptr(g), L.ptr(gw), L.i64(w.numel()), int(self.group_size), L.dtype_code(w),
                                          L.semantics(), L.stream_ptr(w.device))
         L.check(rc, "bdq_nf3_ste_bwd")
@@ -561,7 +561,7 @@ class ShardGatherGroup:
             soffs.append(self.sz_base[t] + soff)
         pc = (ctypes.c_void_p * max(len(peers), 1))(*peers)
         ps = (ctypes.c_void_p * max(len(peers), 1))(*[p + self.ncode for p in peers])
-        with torch.cuda.device(self.device):
+        with L.on(self.device):
             for i in range(0, len(ws), 8):
                 n = len(ws[i:i + 8])
                 rc = L.lib().bdq_int2_shard_encode_multi(
@@ -590,7 +590,7 @@ class ShardGatherGroup:
                                                self.layouts[t], self.pg)
                     self.codes[c0:c0 + codes.numel()] = codes
                     self.sz[s0:s0 + sz.numel()] = sz
-        with torch.cuda.device(self.device):
+        with L.on(self.device):
             if record is not None:
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 e0.record()
@@ -625,7 +625,7 @@ class ShardGatherGroup:
             g = reduce_scatter_rows(g_full.to(self.dtype).contiguous(), self.layouts[t], self.rank, self.pg, average)
             w = w_shard.detach().contiguous()
             gw = torch.empty_like(w)
-            with torch.cuda.device(w.device):
+            with L.on(w.device):
                 rc = L.lib().bdq_int_ste_bwd(L.ptr(w), L.ptr(g), L.ptr(gw), L.i64(w.numel()), int(self.group_size), 2,
                                              L.dtype_code(w), L.semantics(), L.stream_ptr(w.device))
             L.check(rc, "bdq_int_ste_bwd")
@@ -748,7 +748,7 @@ class ShardGradReducer:
         m = len(src)
         cur = torch.cuda.current_stream(self.device)
         self.comm.wait_stream(cur)               # the gradients were produced on the caller's stream
-        with torch.cuda.device(self.device), torch.cuda.stream(self.comm):
+        with L.on(self.device), torch.cuda.stream(self.comm):
             rc = L.lib().bdq_rows_push(m, (ctypes.c_void_p * max(m, 1))(*src), (ctypes.c_void_p * max(m, 1))(*dst),
                                        (ctypes.c_int64 * max(m, 1))(*nb), L.stream_ptr(self.device))
             L.check(rc, "bdq_rows_push")
@@ -773,7 +773,7 @@ class ShardGradReducer:
         cur.wait_event(landed)
         st = L.stream_ptr(self.device)
         res = []
-        with torch.cuda.device(self.device):
+        with L.on(self.device):
             for t, ((_, c), w, g) in enumerate(zip(self.shapes, shards, gs)):
                 r0, r1 = self.spans[t][me]
                 w = w.detach().contiguous()

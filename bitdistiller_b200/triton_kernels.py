@@ -22,7 +22,7 @@ def gemm_w2(x, qweight, scales, qzeros, group_size):
     assert qweight.is_contiguous() and scales.is_contiguous() and qzeros.is_contiguous()
     assert qweight.shape[1] * 16 == IC, "qweight must be [OC, IC/16] int32"
     out = torch.empty((M, OC), dtype=torch.float16, device=x.device)
-    with torch.cuda.device(x.device):
+    with L.on(x.device):
         rc = L.lib().bdq_gemm_w2(L.ptr(x), L.ptr(qweight), L.ptr(scales), L.ptr(qzeros), L.ptr(out), L.i64(M), L.i64(IC),
                                  L.i64(OC), int(group_size), L.stream_ptr(x.device))
     L.check(rc, "bdq_gemm_w2")
