@@ -137,7 +137,7 @@ __global__ void __launch_bounds__(kGmThreads, 1) gemm_w2_kernel(const __grid_con
     uint8_t* smem = gm_smem_raw + ((1024u - (gm_smem_u32(gm_smem_raw) & 1023u)) & 1023u);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kGmStages * kGmStageBytes);
     uint64_t* full_a = bars;                    // [stages] TMA landed
-    uint64_t* full_b = bars + kGmStages;        // [stages] dequant written (256 arrivals)
+    uint64_t* full_b = bars + kGmStages;        // [stages] dequant written (one arrival per producer warp)
     uint64_t* empty = bars + 2 * kGmStages;     // [stages] MMAs that read the stage retired
     uint64_t* tmem_full = bars + 3 * kGmStages;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3 * kGmStages + 1);
@@ -149,7 +149,7 @@ __global__ void __launch_bounds__(kGmThreads, 1) gemm_w2_kernel(const __grid_con
     if (tid == 0) {
         for (int s = 0; s < kGmStages; ++s) {
             gm_mbar_init(&full_a[s], 1);
-            gm_mbar_init(&full_b[s], BTMA ? 1 : kGmN);
+            gm_mbar_init(&full_b[s], BTMA ? 1 : kGmN / 32);   // one arrival per producer warp
             gm_mbar_init(&empty[s], 1);
         }
         gm_mbar_init(tmem_full, 1);
@@ -258,7 +258,8 @@ __global__ void __launch_bounds__(kGmThreads, 1) gemm_w2_kernel(const __grid_con
                 for (int c = 0; c < 8; ++c)   // 16-byte chunk c of row j lives at chunk position c ^ (j % 8)
                     *reinterpret_cast<uint4*>(brow + ((c ^ (j & 7)) << 4)) = make_uint4(o[4 * c], o[4 * c + 1], o[4 * c + 2], o[4 * c + 3]);
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> visible to the MMA (async proxy)
-                gm_mbar_arrive(&full_b[s]);
+                __syncwarp();
+                if (lane == 0) gm_mbar_arrive(&full_b[s]);   // one arrival per warp
             }
             cur = nxt;
 #pragma unroll
