@@ -725,6 +725,11 @@ def secondary_metrics(torch, dev, peak):
                                          "gbs": big["gbs"], "frac_of_hbm_peak": big["frac_of_hbm_peak"],
                                          "what": "the same batch-1 kernel on one lm_head-sized launch (cold, distinct copies)"}
     try:
+        from tools import microbench
+        out["config0_fp32_4096x4096_int2_g128"] = microbench.config0(dev, peak)
+    except Exception as e:
+        out["config0_fp32_4096x4096_int2_g128"] = {"error": f"{type(e).__name__}: {e}"[:300]}
+    try:
         from tools import bench_nf3_gemv
         r = bench_nf3_gemv.run(dev, peak, shapes=[(151936, 4096)])[0]
         out["gemv_nf3_kernel_streaming"] = {"shape": r["shape"], "mb": r["mb"], "us_per_launch": r["us"], "gbs": r["gbs"],

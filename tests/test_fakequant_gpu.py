@@ -289,3 +289,26 @@ def test_errors_and_edge_cases():
     assert bits_equal(dq.cpu(), oracle.int_fakequant(flat.cpu(), 128, 2)["dq"])
     q = SteInt2AsymQuantizer()
     assert q.q_group_size == 64 and q.bit == 2
+
+
+@pytest.mark.parametrize("G", [128, 64, 32])
+@pytest.mark.parametrize("scale", [1.0, 1e-12, 1e-33, 2e-37, 1e31, 1e36])
+def test_nf3_fp32_lean_forward_vs_oracle(scale, G):
+    """The fp32 NF3 forward without auxiliary outputs (shared-divisor IEEE division, one branch-free staircase) against the CPU
+    oracle, bit for bit -- including groups whose scales leave the fast path's exponent range (per-element __fdiv_rn), denormal
+    weights, exact zeros, a group with max == 0 (NaN by the reference's 0/0) and the fused clip."""
+    from bitdistiller_b200 import quantizer as Q
+    w = make_weight("heavy", 96, 1024, torch.float32, 21) * (scale / 0.02)
+    w[3, :G] = w[3, :G].abs() * -1.0          # an all-negative group: max < 0, both scales from the same sign
+    w[5, 7] = 0.0
+    w[6, :G] = torch.minimum(w[6, :G], torch.zeros(G))
+    w[6, 0] = 0.0                              # max == 0 exactly -> NaN group
+    w[7, G:2 * G] = 0.0                        # all-zero group -> NaN group
+    dq = Q.nf3_fakequant(w.to(dev()), G)[0]
+    ref = oracle.nf3_fakequant(w, G)
+    assert bits_equal(dq.cpu(), ref["dq"]), (scale, G)
+    cmax = (w.view(-1, G).amax(1) * 0.7).contiguous()
+    cmin = (w.view(-1, G).amin(1) * 0.8).contiguous()
+    dq = Q.nf3_fakequant(w.to(dev()), G, clip_min=cmin.to(dev()), clip_max=cmax.to(dev()))[0]
+    ref = oracle.nf3_fakequant(w, G, clip_min=cmin, clip_max=cmax)
+    assert bits_equal(dq.cpu(), ref["dq"]), (scale, G, "clip")

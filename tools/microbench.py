@@ -63,3 +63,36 @@ def main():
 
 if __name__ == "__main__":
     main()
+
+
+def config0(dev, peak, nbuf=6):
+    """BASELINE configs[0] on the GPU: pseudo_quantize_tensor int2-g128 on a 4096 x 4096 fp32 weight (134 MB of traffic per
+    call: nearly the 126 MB L2).  Kept L2-cold by rotating `nbuf` input AND output tensors (6 x 64 MB each, 768 MB touched
+    per pass); one pass = `nbuf` launches captured in a CUDA graph; a plain torch copy over the same rotation is the
+    yardstick for what a launch of this size can reach."""
+    from bitdistiller_b200 import quantizer as Q
+    n = 4096 * 4096
+    ws = [torch.randn(4096, 4096, device=dev) * 0.02 for _ in range(nbuf)]
+    outs = [torch.empty_like(w) for w in ws]
+
+    def run_q():
+        for w, o in zip(ws, outs):
+            Q.int_fakequant(w, 2, 128, 0, out=o)
+
+    def run_copy():
+        for w, o in zip(ws, outs):
+            o.copy_(w)
+
+    res = {}
+    for name, fn in (("pseudo_quantize_tensor", run_q), ("torch_copy", run_copy)):
+        fn()
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            fn()
+        t = timeit(lambda i: g.replay(), 1, iters=10) / nbuf
+        res[name] = {"us": t * 1e6, "gbs": n * 8 / t / 1e9, "frac_of_hbm_peak": n * 8 / t / 1e9 / peak}
+    res["vs_copy"] = res["torch_copy"]["us"] / res["pseudo_quantize_tensor"]["us"]
+    res["what"] = ("configs[0] shape on the GPU, fp32, 8 B/weight; L2-cold: 6 rotating input and 6 rotating output tensors (768 MB per pass), "
+                   "6 launches per CUDA graph; torch_copy = dst.copy_(src) over the same rotation")
+    return res
