@@ -284,11 +284,18 @@ __device__ __noinline__ void nf3_bwd_slow_global(const void* w, const void* gy, 
     }
 }
 
-template <int DT>
+// MS: the incoming gradient is gy + ex.p[0] + ... + ex.p[ex.n - 1] (fused reduce-scatter for FSDP2 shards, see fakequant_thr.cu:
+// accumulated in that order with one rounding to T per addition; the op-by-op fallback reads the sum back from its own slot of gw)
+struct Nf3GySrcs {
+    const uint8_t* p[7];
+    int n;
+};
+
+template <int DT, bool MS>
 __global__ void __launch_bounds__(kNf3ThrThreads) nf3_thr_bwd_kernel(const uint8_t* __restrict__ w, const uint8_t* __restrict__ gy,
-                                                                     uint8_t* __restrict__ gw, int64_t nchunk,
+                                                                     uint8_t* gw, int64_t nchunk,
                                                                      const __grid_constant__ Nf3Tables tab,
-                                                                     const __grid_constant__ Nf3Stair st) {
+                                                                     const __grid_constant__ Nf3Stair st, const Nf3GySrcs ex) {
     using P = P2<DT>;
     using h2 = typename P::h2;
     constexpr int LPG = 4, R = 2, NP = 1;
@@ -313,6 +320,19 @@ __global__ void __launch_bounds__(kNf3ThrThreads) nf3_thr_bwd_kernel(const uint8
         } else {
 #pragma unroll
             for (int i = 0; i < 8; ++i) rx[0].r[i] = rx[1].r[i] = rg[0].r[i] = rg[1].r[i] = 0;
+        }
+        if constexpr (MS) {
+            if (valid) {
+#pragma unroll 1
+                for (int sidx = 0; sidx < ex.n; ++sidx) {
+                    const U8 a0 = ldg256(ex.p[sidx] + idx * 64), a1 = ldg256(ex.p[sidx] + idx * 64 + 32);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        rg[0].r[i] = P::bits(__hadd2(P::from_bits(rg[0].r[i]), P::from_bits(a0.r[i])));
+                        rg[1].r[i] = P::bits(__hadd2(P::from_bits(rg[1].r[i]), P::from_bits(a1.r[i])));
+                    }
+                }
+            }
         }
         float mx, mn, mx1, mn1;
         vec_minmax16<DT>(rx[0], mx, mn);
@@ -365,26 +385,45 @@ __global__ void __launch_bounds__(kNf3ThrThreads) nf3_thr_bwd_kernel(const uint8
                 stg256(gw + idx * 64 + 32, out[1]);
             }
         } else {
-            nf3_bwd_slow_global<DT>(w, gy, gw, idx * 32, valid, mx, mn, tab);
+            const uint8_t* gsl = gy;
+            if constexpr (MS) {   // park the summed gradient of this lane's 32 elements in its own slot of gw (read and rewritten by this thread only)
+                gsl = gw;
+                if (valid) {
+                    stg256(gw + idx * 64, rg[0]);
+                    stg256(gw + idx * 64 + 32, rg[1]);
+                }
+            }
+            nf3_bwd_slow_global<DT>(w, gsl, gw, idx * 32, valid, mx, mn, tab);
         }
     }
 }
 
 // Returns true if the threshold backward was launched (16-bit dtype, group 128, 32-byte aligned).
-bool launch_nf3_thr_bwd(const void* w, const void* gy, void* gw, int64_t n, int G, int dtype, int sem, cudaStream_t st) {
+bool launch_nf3_thr_bwd_ms(const void* w, const void* gy, void* gw, int64_t n, int G, int dtype, int sem, cudaStream_t st, int n_extra,
+                           const void* const* extra) {
     if ((dtype != kBF16 && dtype != kF16) || G != 128) return false;
     if (((uintptr_t)w % 32) || ((uintptr_t)gy % 32) || ((uintptr_t)gw % 32) || (n % 128)) return false;
+    if (n_extra < 0 || n_extra > 7) return false;
+    Nf3GySrcs ex;
+    ex.n = n_extra;
+    for (int i = 0; i < 7; ++i) {
+        ex.p[i] = i < n_extra ? (const uint8_t*)extra[i] : nullptr;
+        if (i < n_extra && (!extra[i] || ((uintptr_t)extra[i] % 32))) return false;
+    }
     const Nf3Tables tab = make_tables(dtype, sem);
     const int64_t nchunk = n / 32;
     const int64_t nb = nf3_thr_blocks(nchunk);
-    if (dtype == kBF16) {
-        nf3_thr_bwd_kernel<kBF16><<<wave_grid(nf3_thr_bwd_kernel<kBF16>, kNf3ThrThreads, nb, 6), kNf3ThrThreads, 0, st>>>((const uint8_t*)w, (const uint8_t*)gy, (uint8_t*)gw, nchunk,
-                                                                    tab, make_stair(tab, kBF16));
-    } else {
-        nf3_thr_bwd_kernel<kF16><<<wave_grid(nf3_thr_bwd_kernel<kF16>, kNf3ThrThreads, nb, 6), kNf3ThrThreads, 0, st>>>((const uint8_t*)w, (const uint8_t*)gy, (uint8_t*)gw, nchunk, tab,
-                                                                   make_stair(tab, kF16));
-    }
+#define BDQ_NB(DTT, MSS)                                                                                                              \
+    nf3_thr_bwd_kernel<DTT, MSS><<<wave_grid(nf3_thr_bwd_kernel<DTT, MSS>, kNf3ThrThreads, nb, 6), kNf3ThrThreads, 0, st>>>(           \
+        (const uint8_t*)w, (const uint8_t*)gy, (uint8_t*)gw, nchunk, tab, make_stair(tab, DTT), ex)
+    if (dtype == kBF16) { if (n_extra) BDQ_NB(kBF16, true); else BDQ_NB(kBF16, false); }
+    else { if (n_extra) BDQ_NB(kF16, true); else BDQ_NB(kF16, false); }
+#undef BDQ_NB
     return true;
+}
+
+bool launch_nf3_thr_bwd(const void* w, const void* gy, void* gw, int64_t n, int G, int dtype, int sem, cudaStream_t st) {
+    return launch_nf3_thr_bwd_ms(w, gy, gw, n, G, dtype, sem, st, 0, nullptr);
 }
 
 }  // namespace bdq

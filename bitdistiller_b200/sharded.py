@@ -420,7 +420,8 @@ class ShardGatherNF3:
     (quantization/quantizer.py:184-242) bit for bit on every rank, moving 0.41 B/weight instead of 2 (bdq_nf3_shard_encode
     stores 3-bit level indices + the two scales of every group into every rank's symmetric-memory buffer, one barrier,
     bdq_nf3_shard_decode).  `backward`: reduce-scatter of the gradient w.r.t. the quantised weight, then bdq_nf3_ste_bwd on the
-    shard (the NF3 STE backward is linear in the incoming gradient and group-local, like the integer one)."""
+    shard (the NF3 STE backward is linear in the incoming gradient and group-local, like the integer one); after
+    enable_fused_backward() both are one pass over NVLink peer memory (ShardGradReducer)."""
 
     def __init__(self, rows, cols, group_size, dtype, device, group=None, symmetric=True):
         self.rows, self.cols, self.group_size, self.dtype, self.device = rows, cols, group_size, dtype, torch.device(device)
@@ -479,9 +480,18 @@ class ShardGatherNF3:
         self.codes, self.sc = codes, sc
         return dq
 
+    def enable_fused_backward(self):
+        """Use ShardGradReducer(quant="nf3") for `backward`: gradient rows pushed over NVLink peer memory + the multi-source NF3
+        STE backward (bdq_nf3_ste_bwd_nsrc), no collective, the reduced gradient never materialised."""
+        if self.symmetric and getattr(self, "reducer", None) is None:
+            self.reducer = ShardGradReducer([(self.rows, self.cols)], self.group_size, self.dtype, self.device, self.pg, quant="nf3")
+        return getattr(self, "reducer", None) is not None
+
     @torch.no_grad()
     def backward(self, w_shard, g_full, average=False):
         from . import _lib as L
+        if getattr(self, "reducer", None) is not None and not average:
+            return self.reducer.backward([w_shard], [g_full.to(self.dtype)])[0]
         g = reduce_scatter_rows(g_full.to(self.dtype).contiguous(), self.layout, self.rank, self.pg, average)
         w = w_shard.detach().contiguous()
         gw = torch.empty_like(w)
@@ -693,13 +703,16 @@ class ShardGradReducer:
          r's dim-0 shard into r's symmetric-memory inbox -- the kernel's stores are the NVLink transfer, one launch per
          parameter group;
       2. one symmetric-memory barrier (the inbox is double-buffered across calls, like ShardGatherGroup's payload);
-      3. `bdq_int_ste_bwd_nsrc` per tensor: the STE backward of the shard with the incoming gradient summed on the fly from the
+      3. `bdq_int_ste_bwd_nsrc` (`bdq_nf3_ste_bwd_nsrc` with quant="nf3") per tensor: the STE backward of the shard with the incoming gradient summed on the fly from the
          rank's own rows and the n-1 inbox slots, in rank order, one rounding to the dtype per addition (for two ranks: the
          rounded exact sum, bit-equal to an NCCL reduce-scatter; in general what a ring reduction in that dtype computes).
     The reduced gradient is never materialised.  `shapes`: [(rows, cols)] of the group's tensors."""
 
-    def __init__(self, shapes, group_size, dtype, device, group=None):
+    def __init__(self, shapes, group_size, dtype, device, group=None, quant="int2"):
         import torch.distributed._symmetric_memory as symm_mem
+        if quant not in ("int2", "nf3"):
+            raise ValueError("ShardGradReducer: quant must be 'int2' (SteInt2AsymQuantizer) or 'nf3' (SteN2F3Quantizer)")
+        self.quant = quant
         self.shapes, self.group_size, self.dtype, self.device, self.pg = list(shapes), group_size, dtype, torch.device(device), group
         self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
         if not 2 <= self.world <= 8:
@@ -784,9 +797,14 @@ class ShardGradReducer:
                         srcs.append(g.data_ptr() + r0 * c * es)
                     else:
                         srcs.append(self.inbox.data_ptr() + base + self._slot_of(k, me) * self.slot + self.off[me][t])
-                rc = L.lib().bdq_int_ste_bwd_nsrc(L.ptr(w), n, (ctypes.c_void_p * n)(*srcs), L.ptr(gw), L.i64(w.numel()),
-                                                  int(self.group_size), 2, L.dtype_code(w), L.semantics(), st)
-                L.check(rc, "bdq_int_ste_bwd_nsrc")
+                if self.quant == "nf3":
+                    rc = L.lib().bdq_nf3_ste_bwd_nsrc(L.ptr(w), n, (ctypes.c_void_p * n)(*srcs), L.ptr(gw), L.i64(w.numel()),
+                                                      int(self.group_size), L.dtype_code(w), L.semantics(), st)
+                    L.check(rc, "bdq_nf3_ste_bwd_nsrc")
+                else:
+                    rc = L.lib().bdq_int_ste_bwd_nsrc(L.ptr(w), n, (ctypes.c_void_p * n)(*srcs), L.ptr(gw), L.i64(w.numel()),
+                                                      int(self.group_size), 2, L.dtype_code(w), L.semantics(), st)
+                    L.check(rc, "bdq_int_ste_bwd_nsrc")
                 res.append(gw)
         self._done = torch.cuda.Event()
         self._done.record(cur)

@@ -231,6 +231,49 @@ def test_ste_bwd_multi_source_and_push(dname, nsrc):
 
 
 @pytest.mark.parametrize("dname", ["bf16", "f16"])
+@pytest.mark.parametrize("nsrc", [2, 3, 8])
+def test_nf3_ste_bwd_multi_source(dname, nsrc):
+    """bdq_nf3_ste_bwd_nsrc: summing `nsrc` gradient sources on the fly equals the sequential sum (one rounding per addition,
+    source order) followed by bdq_nf3_ste_bwd, bit for bit -- including groups that take the op-by-op path (huge dynamic
+    range, an all-positive group, a NaN group with max == 0) and NaN gradients."""
+    import ctypes
+
+    from bitdistiller_b200 import _lib as L
+    dt = {"bf16": torch.bfloat16, "f16": torch.float16}[dname]
+    dev = torch.device("cuda:0")
+    rows, cols, G = 96, 1024, 128
+    g = torch.Generator().manual_seed(100 + nsrc)
+    w = (torch.randn(rows, cols, generator=g) * 0.02).to(dt)
+    w[3, :128] *= 1e-6
+    w[3, 5] = 30000.0 if dname == "f16" else 3e30      # op-by-op path
+    w[4, 128:256] = w[4, 128:256].abs() + 0.001        # all-positive group
+    w[5, :128] = torch.minimum(w[5, :128], torch.zeros(128, dtype=dt))
+    w[5, 0] = 0.0                                      # max == 0: NaN group
+    w = w.to(dev)
+    srcs = [torch.randn(rows, cols, generator=g).to(dt).to(dev) for _ in range(nsrc)]
+    srcs[-1][7, 9] = float("nan")
+    st = L.stream_ptr(dev)
+    gw = torch.empty_like(w)
+    ptrs = [t_.data_ptr() for t_ in srcs]
+    L.check(L.lib().bdq_nf3_ste_bwd_nsrc(L.ptr(w), nsrc, (ctypes.c_void_p * nsrc)(*ptrs), L.ptr(gw), L.i64(w.numel()), G,
+                                         L.dtype_code(w), L.semantics(), st), "nsrc")
+    acc = srcs[0].clone()
+    for s_ in srcs[1:]:
+        acc = (acc.float() + s_.float()).to(dt)
+    ref = torch.empty_like(w)
+    L.check(L.lib().bdq_nf3_ste_bwd(L.ptr(w), L.ptr(acc), L.ptr(ref), L.i64(w.numel()), G, L.dtype_code(w), L.semantics(), st), "bwd")
+    torch.cuda.synchronize()
+    same = (gw.view(torch.int16) == ref.view(torch.int16)) | (gw.isnan() & ref.isnan())
+    assert bool(same.all()), int((~same).sum())
+    with pytest.raises(L.BdqError):
+        L.check(L.lib().bdq_nf3_ste_bwd_nsrc(L.ptr(w), 9, (ctypes.c_void_p * 9)(*([ptrs[0]] * 9)), L.ptr(gw), L.i64(w.numel()), G,
+                                             L.dtype_code(w), L.semantics(), st), "nsrc")
+    with pytest.raises(L.BdqError):     # group 64 has no multi-source kernel
+        L.check(L.lib().bdq_nf3_ste_bwd_nsrc(L.ptr(w), 2, (ctypes.c_void_p * 2)(*ptrs[:2]), L.ptr(gw), L.i64(w.numel()), 64,
+                                             L.dtype_code(w), L.semantics(), st), "nsrc")
+
+
+@pytest.mark.parametrize("dname", ["bf16", "f16"])
 @pytest.mark.parametrize("G", [128, 64, 32])
 def test_nf3_shard_payload_roundtrip(dname, G):
     """bdq_nf3_shard_encode / _decode (the NF3 payload of quantise-before-all-gather): level indices against the oracle's NF3

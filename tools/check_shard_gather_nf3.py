@@ -33,10 +33,19 @@ if world > 1:
         SteN2F3Quantizer(128)(x).backward(gsum)
         same = (gw.view(torch.int16) == x.grad[a:b].view(torch.int16)) | (gw.isnan() & x.grad[a:b].isnan())
         ok = ok and (bool(same.all()) if world == 2 else float((gw.float() - x.grad[a:b].float()).abs().max()) < 1e-2)
+        if sym and sg.enable_fused_backward():   # gradient push over NVLink + bdq_nf3_ste_bwd_nsrc: same result, no collective
+            for rep in range(2):
+                gw2 = sg.backward(full[a:b].contiguous(), g)
+                torch.cuda.synchronize()
+                same2 = (gw2.view(torch.int16) == x.grad[a:b].view(torch.int16)) | (gw2.isnan() & x.grad[a:b].isnan())
+                okf = bool(same2.all()) if world == 2 else float((gw2.float() - x.grad[a:b].float()).abs().max()) < 1e-2
+                if not okf:
+                    print(f"rank {rank}: fused NF3 backward mismatch on [{rows}, {cols}] rep {rep}: {int((~same2).sum())} elements", flush=True)
+                ok = ok and okf
     flag = torch.tensor([int(ok)], device=dev)
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     ok = bool(flag.item())
-res = {"world": world, "nf3_forward_bit_equal_and_backward_rows_equal": ok}
+res = {"world": world, "nf3_forward_bit_equal_and_backward_rows_equal_incl_fused_backward": ok}
 if rank == 0:
     n = 4 * 4096 * 4096 + 3 * 11008 * 4096
     ws = [(torch.randn(n // 4096, 4096, device=dev) * 0.02).bfloat16() for _ in range(3)]
