@@ -49,7 +49,61 @@ void run(const char* name) {
     cudaFree(cyc);
 }
 
+// Do the pipes overlap?  Per iteration and warp: NA independent PRMTs (ALU pipe), NF independent IMADs (FMA pipe), NT IMMA.16832
+// (tensor pipe, 2 accumulator chains).  If the pipes overlap the time is the maximum of the three, if not their sum.
+template <int NA, int NF, int NT>
+__global__ void mixk(int iters, uint32_t* out, long long* cyc, uint32_t s0) {
+    uint32_t v[8], f[8];
+    int acc[2][4] = {{0, 0, 0, 0}, {0, 0, 0, 0}};
+    for (int c = 0; c < 8; ++c) { v[c] = threadIdx.x * 2654435761u + c; f[c] = threadIdx.x * 40503u + c; }
+    const uint32_t a = s0 ^ 0x01234567u, b = s0 ^ 0x89abcdefu;
+    long long t0 = clock64();
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+            if (c < NA) asm volatile("prmt.b32 %0, %1, %2, %0;" : "+r"(v[c]) : "r"(a), "r"(b));
+            if (c < NF) asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(f[c]) : "r"(a), "r"(b));
+            if (c < NT)
+                asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.s8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                             : "+r"(acc[c & 1][0]), "+r"(acc[c & 1][1]), "+r"(acc[c & 1][2]), "+r"(acc[c & 1][3])
+                             : "r"(a), "r"(b), "r"(a), "r"(b), "r"(a), "r"(b));
+        }
+    }
+    long long t1 = clock64();
+    uint32_t s = 0;
+    for (int c = 0; c < 8; ++c) s ^= v[c] ^ f[c];
+    for (int c = 0; c < 4; ++c) s ^= (uint32_t)(acc[0][c] ^ acc[1][c]);
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+    if (threadIdx.x == 0 && blockIdx.x == 0) *cyc = t1 - t0;
+}
+
+template <int NA, int NF, int NT>
+void mix(const char* name) {
+    uint32_t* out;
+    long long* cyc;
+    cudaMalloc(&out, 1 << 22);
+    cudaMalloc(&cyc, 8);
+    const int iters = 4000, threads = 4 * 4 * 32;
+    mixk<NA, NF, NT><<<148, threads>>>(iters, out, cyc, 0);
+    mixk<NA, NF, NT><<<148, threads>>>(iters, out, cyc, 0);
+    cudaDeviceSynchronize();
+    long long h;
+    cudaMemcpy(&h, cyc, 8, cudaMemcpyDeviceToHost);
+    printf("%-44s %.1f cycles per iteration per scheduler (4 warps)\n", name, (double)h / iters);
+    cudaFree(out);
+    cudaFree(cyc);
+}
+
 int main() {
+    mix<8, 0, 0>("8 PRMT");
+    mix<0, 8, 0>("8 IMAD");
+    mix<0, 0, 2>("2 IMMA.16832");
+    mix<8, 8, 0>("8 PRMT + 8 IMAD");
+    mix<8, 0, 2>("8 PRMT + 2 IMMA");
+    mix<0, 8, 2>("8 IMAD + 2 IMMA");
+    mix<8, 8, 2>("8 PRMT + 8 IMAD + 2 IMMA");
+    mix<4, 4, 2>("4 PRMT + 4 IMAD + 2 IMMA");
+
     run<0>("PRMT (register selector)");
     run<1>("LOP3");
     run<2>("SHF (shr imm)");
