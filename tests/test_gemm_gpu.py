@@ -130,3 +130,43 @@ def test_gemm_f16_tcgen05_vs_fp32_matmul(m, oc, ic):
     _check(out, ref, x, w)
     with pytest.raises(L.BdqError):
         gemm_f16(x[:, :ic - 8].contiguous(), w[:, :ic - 8].contiguous())
+
+
+@pytest.mark.parametrize("tile", ["auto", "11", "21", "12", "22"])
+def test_gemm_partial_tiles_write_nothing_outside(tile, monkeypatch):
+    """Partial last tiles in both directions (M = 200: a 128-row tile + 72 rows; OC = 1056 = 8 x 128 + 32) through the C ABI with
+    the output inside a larger sentinel-filled buffer: the values match an fp32 matmul of the dequantised weights and not one
+    element around the output is touched.  BDQ_GEMM_TILE is read once per process, so the forced tiles run in a subprocess."""
+    import subprocess
+    import sys
+    code = r"""
+import ctypes, torch
+from bitdistiller_b200 import _lib as L, quantizer as Q
+from bitdistiller_b200.qmodule import pack_wq
+dev = torch.device("cuda:0")
+M, IC, OC, PAD = 200, 1024, 1056, 4096
+g = torch.Generator(device=dev).manual_seed(5)
+w = (torch.randn(OC, IC, device=dev, generator=g) * 0.03).half()
+dq, s, z, _ = Q.int_fakequant(w, 2, 128, 0, want_scale_zp=True)
+qw, qz, qs = pack_wq(dq, s.view(OC, -1), z.view(OC, -1), 2, 128)
+x = torch.randn(M, IC, device=dev, generator=g).half()
+big = torch.full((PAD + M * OC + PAD,), 777.0, dtype=torch.float16, device=dev)
+out = big[PAD:PAD + M * OC]
+rc = L.lib().bdq_gemm_w2(L.ptr(x), L.ptr(qw), L.ptr(qs), L.ptr(qz), ctypes.c_void_p(out.data_ptr()), L.i64(M), L.i64(IC), L.i64(OC), 128,
+                         L.stream_ptr(dev))
+L.check(rc, "bdq_gemm_w2")
+torch.cuda.synchronize()
+ref = x.float() @ dq.float().T
+err = float((out.view(M, OC).float() - ref).norm() / ref.norm())
+assert err < 2e-3, err
+assert bool((big[:PAD] == 777.0).all()) and bool((big[PAD + M * OC:] == 777.0).all()), "wrote outside the output"
+print("ok", err)
+"""
+    import os
+    env = dict(os.environ)
+    env.pop("BDQ_GEMM_TILE", None)
+    if tile != "auto":
+        env["BDQ_GEMM_TILE"] = tile
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-c", code], cwd=root, env=env, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "ok" in r.stdout, r.stdout[-500:] + r.stderr[-1500:]

@@ -143,3 +143,27 @@ def test_gemv_nf3_stream_nonfinite():
     assert bool(P.gemv_nf3(x2, qw, qh, sc, 128).isnan().all())
     z = torch.zeros_like(sc)                      # all-zero scales: zero output, not NaN
     assert float(P.gemv_nf3(x, qw, qh, z, 128).abs().max()) == 0.0
+
+
+def test_gemv_nf3_writes_nothing_outside_the_output():
+    """Both NF3 GEMV kernels through the C ABI with the output inside a sentinel-filled buffer (ragged OC for the pair lookup,
+    a partial last K window for the streaming kernel)."""
+    import ctypes
+
+    from bitdistiller_b200 import _lib as L
+    from bitdistiller_b200 import nf3_packed as P
+    for oc, ic in [(1040, 2176), (1038 // 2 * 2 - 2, 1024)]:     # 1040 = 65 x 16: streaming kernel; 1036: pair lookup
+        w = (make_weight("randn", oc + (-oc) % 2, ic, torch.float16, 9).float() * 1.7).half().to(dev)[:oc].contiguous()
+        qw, qh, sc = P.pack_nf3(w, 128)
+        dq = P.dequant_nf3(qw, qh, sc, 128)
+        B, PAD = 3, 512
+        x = torch.randn(B, ic, generator=torch.Generator().manual_seed(2)).half().to(dev)
+        big = torch.full((PAD + B * oc + PAD,), 777.0, dtype=torch.float16, device=dev)
+        out = big[PAD:PAD + B * oc]
+        rc = L.lib().bdq_gemv_nf3(L.ptr(x), L.ptr(qw), L.ptr(qh), L.ptr(sc), ctypes.c_void_p(out.data_ptr()), L.i64(B), L.i64(ic), L.i64(oc),
+                                  128, L.stream_ptr(dev))
+        L.check(rc, "bdq_gemv_nf3")
+        torch.cuda.synchronize()
+        ref = x.double() @ dq.double().T
+        assert float((out.view(B, oc).double() - ref).norm() / ref.norm()) < 2e-3
+        assert bool((big[:PAD] == 777.0).all()) and bool((big[PAD + B * oc:] == 777.0).all()), (oc, ic)
