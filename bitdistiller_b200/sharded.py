@@ -13,6 +13,8 @@
 The collectives go through torch.distributed (NCCL on GPUs; the same code runs on gloo/CPU tensors, which is how the
 host-side logic is tested without a GPU).  Nothing here touches the kernels' arithmetic.
 """
+import os
+
 import torch
 import torch.distributed as dist
 import torch.nn as nn
@@ -740,7 +742,10 @@ class ShardGradReducer:
 
         from . import _lib as L
         if not hasattr(self, "comm"):
-            self.comm = torch.cuda.Stream(self.device)
+            # high priority: the push kernel's CTAs are placed before the HBM-bound STE launches they overlap with, so the NVLink
+            # transfer (the longer of the two) is never the one that waits for SM slots (BDQ_PUSH_PRIORITY=0: default priority)
+            prio = -1 if os.environ.get("BDQ_PUSH_PRIORITY", "-1") != "0" else 0
+            self.comm = torch.cuda.Stream(self.device, priority=prio)
             self._done = None                 # event: the STE launches of the previous `finish` have completed
         base = self.flip * self.half
         self.flip ^= 1
