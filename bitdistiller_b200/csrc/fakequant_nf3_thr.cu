@@ -135,11 +135,17 @@ __global__ void __launch_bounds__(kNf3ThrThreads) nf3_thr_fwd_kernel(const uint8
                 const int64_t g = idx / LPG;
                 clo = load_scalar<DT>(cmin, g);
                 chi = load_scalar<DT>(cmax, g);
-                const h2 l2 = P::dup(clo), u2 = P::dup(chi);
+                // The clamp itself is only needed when a bound lies on the wrong side of zero.  With clo <= 0 <= chi the extremes
+                // of the clamped group are the clamped extremes (clamp is monotone), an element above chi sits on the top step of
+                // the staircase whether it is clamped to chi = max -> q = 1 or not, one below clo on the bottom step: the level
+                // selection on the raw elements is the selection on the clamped ones, and 32 packed min / max per lane go away.
+                if (!(clo <= 0.f && chi >= 0.f)) {   // uniform per group
+                    const h2 l2 = P::dup(clo), u2 = P::dup(chi);
 #pragma unroll
-                for (int v = 0; v < 2; ++v)
+                    for (int v = 0; v < 2; ++v)
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) raw[v].r[i] = P::bits(__hmin2(__hmax2(P::from_bits(raw[v].r[i]), l2), u2));
+                        for (int i = 0; i < 8; ++i) raw[v].r[i] = P::bits(__hmin2(__hmax2(P::from_bits(raw[v].r[i]), l2), u2));
+                }
             }
         }
         float mx, mn, mx1, mn1;
@@ -147,6 +153,10 @@ __global__ void __launch_bounds__(kNf3ThrThreads) nf3_thr_fwd_kernel(const uint8
         vec_minmax16<DT>(raw[1], mx1, mn1);
         mx = group_max<LPG>(fmaxf(mx, mx1));
         mn = group_min<LPG>(fminf(mn, mn1));
+        if constexpr (CLIP) {
+            mx = fminf(fmaxf(mx, clo), chi);
+            mn = fminf(fmaxf(mn, clo), chi);
+        }
         const float sp = fabsf(mx), sn = fabsf(mn);
         uint32_t sh[LPG][NP];
         const bool ok = nf3_group_thresholds<DT, LPG>(my, st.mask, sp, sn, lig, gbase, sh);
