@@ -257,9 +257,14 @@ __global__ void __launch_bounds__(kGmThreads, 1) gemm_w2_kernel(const __grid_con
 #pragma unroll
                 for (int c = 0; c < 8; ++c)   // 16-byte chunk c of row j lives at chunk position c ^ (j % 8)
                     *reinterpret_cast<uint4*>(brow + ((c ^ (j & 7)) << 4)) = make_uint4(o[4 * c], o[4 * c + 1], o[4 * c + 2], o[4 * c + 3]);
-                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> visible to the MMA (async proxy)
-                __syncwarp();
-                if (lane == 0) gm_mbar_arrive(&full_b[s]);   // one arrival per warp
+            }
+            // ONE proxy fence for the pair of rows: the fence (MEMBAR + FENCE.VIEW.ASYNC) is where the producer warps spend a fifth of
+            // their time (ncu), so it is paid once per two k blocks; the first stage's arrival waits for the second row's stores
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> visible to the MMA (async proxy)
+            __syncwarp();
+            if (lane == 0) {   // one arrival per warp and stage
+                gm_mbar_arrive(&full_b[(gp * 2) % kGmStages]);
+                gm_mbar_arrive(&full_b[(gp * 2 + 1) % kGmStages]);
             }
             cur = nxt;
 #pragma unroll
