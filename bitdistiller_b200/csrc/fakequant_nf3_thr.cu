@@ -259,13 +259,13 @@ __device__ __forceinline__ uint32_t nf3_bwd_fix(uint32_t g, uint32_t x, uint32_t
 // op-by-op path for one lane's 32 elements (its group = 4 lanes); called by the whole warp
 template <int DT>
 __device__ __noinline__ void nf3_bwd_slow_global(const void* w, const void* gy, void* gw, int64_t e0, bool valid, float mx,
-                                                 float mn, const Nf3Tables& t) {
+                                                 float mn, const Nf3Tables& t, int n_el = 32) {
     const Nf3Q p = nf3_group_params(mx, mn);
     float Gp = 0.f, Gn = 0.f;
     int cnt = 0;
     if (valid) {
 #pragma unroll 1
-        for (int i = 0; i < 32; ++i) {
+        for (int i = 0; i < n_el; ++i) {
             const float x = load_scalar<DT>(w, e0 + i), g = load_scalar<DT>(gy, e0 + i);
             float q, y;
             int code;
@@ -283,7 +283,7 @@ __device__ __noinline__ void nf3_bwd_slow_global(const void* w, const void* gy, 
     const float tmax = sgx * Gp / (float)(cnt & 0xffff), tmin = sgn * Gn / (float)(cnt >> 16);
     if (valid) {
 #pragma unroll 1
-        for (int i = 0; i < 32; ++i) {
+        for (int i = 0; i < n_el; ++i) {
             const float x = load_scalar<DT>(w, e0 + i);
             float r = load_scalar<DT>(gy, e0 + i);
             if (x == mx) r += tmax;
@@ -301,14 +301,48 @@ struct Nf3GySrcs {
     int n;
 };
 
-template <int DT, bool MS>
+// EPL = elements per lane (32 / 16 / 8): a group is always one quad of lanes, so G = 4 * EPL = 128 / 64 / 32 share the fragment
+// trick above unchanged (G = 64 is the group size of every train script of the reference, scripts/train/train.sh:52).
+template <int EPL>
+__device__ __forceinline__ void nf3_lane_load(const uint8_t* p, int64_t idx, uint32_t* r) {
+    if constexpr (EPL == 32) {
+        const U8 a = ldg256(p + idx * 64), b = ldg256(p + idx * 64 + 32);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { r[i] = a.r[i]; r[8 + i] = b.r[i]; }
+    } else if constexpr (EPL == 16) {
+        const U8 a = ldg256(p + idx * 32);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) r[i] = a.r[i];
+    } else {
+        asm volatile("ld.global.nc.L1::no_allocate.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "l"(p + idx * 16));
+    }
+}
+template <int EPL>
+__device__ __forceinline__ void nf3_lane_store(uint8_t* p, int64_t idx, const uint32_t* r) {
+    if constexpr (EPL == 32) {
+        U8 a, b;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { a.r[i] = r[i]; b.r[i] = r[8 + i]; }
+        stg256(p + idx * 64, a);
+        stg256(p + idx * 64 + 32, b);
+    } else if constexpr (EPL == 16) {
+        U8 a;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) a.r[i] = r[i];
+        stg256(p + idx * 32, a);
+    } else {
+        asm volatile("st.global.v4.b32 [%0], {%1,%2,%3,%4};" ::"l"(p + idx * 16), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]) : "memory");
+    }
+}
+
+template <int DT, bool MS, int EPL>
 __global__ void __launch_bounds__(kNf3ThrThreads) nf3_thr_bwd_kernel(const uint8_t* __restrict__ w, const uint8_t* __restrict__ gy,
                                                                      uint8_t* gw, int64_t nchunk,
                                                                      const __grid_constant__ Nf3Tables tab,
                                                                      const __grid_constant__ Nf3Stair st, const Nf3GySrcs ex) {
     using P = P2<DT>;
     using h2 = typename P::h2;
-    constexpr int LPG = 4, R = 2, NP = 1;
+    constexpr int LPG = 4, R = 2, NP = 1, NR = EPL / 2;
     const int lane = threadIdx.x & 31;
     const int lig = lane & 3, gbase = lane & ~3, grp = lane >> 2;
     const int64_t warp = (int64_t)blockIdx.x * (kNf3ThrThreads / 32) + (threadIdx.x >> 5);
@@ -321,34 +355,33 @@ __global__ void __launch_bounds__(kNf3ThrThreads) nf3_thr_bwd_kernel(const uint8
     for (int64_t wc = warp; wc < nwc; wc += nwarps) {
         const int64_t idx = wc * 32 + lane;
         const bool valid = idx < nchunk;
-        U8 rx[2], rg[2];
+        uint32_t rx[NR], rg[NR];
         if (valid) {
-            rx[0] = ldg256(w + idx * 64);
-            rx[1] = ldg256(w + idx * 64 + 32);
-            rg[0] = ldg256(gy + idx * 64);
-            rg[1] = ldg256(gy + idx * 64 + 32);
+            nf3_lane_load<EPL>(w, idx, rx);
+            nf3_lane_load<EPL>(gy, idx, rg);
         } else {
 #pragma unroll
-            for (int i = 0; i < 8; ++i) rx[0].r[i] = rx[1].r[i] = rg[0].r[i] = rg[1].r[i] = 0;
+            for (int i = 0; i < NR; ++i) rx[i] = rg[i] = 0;
         }
         if constexpr (MS) {
             if (valid) {
 #pragma unroll 1
                 for (int sidx = 0; sidx < ex.n; ++sidx) {
-                    const U8 a0 = ldg256(ex.p[sidx] + idx * 64), a1 = ldg256(ex.p[sidx] + idx * 64 + 32);
+                    uint32_t a[NR];
+                    nf3_lane_load<EPL>(ex.p[sidx], idx, a);
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        rg[0].r[i] = P::bits(__hadd2(P::from_bits(rg[0].r[i]), P::from_bits(a0.r[i])));
-                        rg[1].r[i] = P::bits(__hadd2(P::from_bits(rg[1].r[i]), P::from_bits(a1.r[i])));
-                    }
+                    for (int i = 0; i < NR; ++i) rg[i] = P::bits(__hadd2(P::from_bits(rg[i]), P::from_bits(a[i])));
                 }
             }
         }
-        float mx, mn, mx1, mn1;
-        vec_minmax16<DT>(rx[0], mx, mn);
-        vec_minmax16<DT>(rx[1], mx1, mn1);
-        mx = group_max<LPG>(fmaxf(mx, mx1));
-        mn = group_min<LPG>(fminf(mn, mn1));
+        h2 a2 = P::from_bits(rx[0]), b2 = a2;
+#pragma unroll
+        for (int i = 1; i < NR; ++i) {
+            a2 = __hmax2(a2, P::from_bits(rx[i]));
+            b2 = __hmin2(b2, P::from_bits(rx[i]));
+        }
+        const float mx = group_max<LPG>(fmaxf(P::lo(a2), P::hi(a2)));
+        const float mn = group_min<LPG>(fminf(P::lo(b2), P::hi(b2)));
         const float sp = fabsf(mx), sn = fabsf(mn);
         uint32_t sh[LPG][NP];
         bool ok = nf3_group_thresholds<DT, LPG>(my, st.mask, sp, sn, lig, gbase, sh);
@@ -361,20 +394,18 @@ __global__ void __launch_bounds__(kNf3ThrThreads) nf3_thr_bwd_kernel(const uint8
             const h2 zero2 = P::from_bits(0u);
             float dy[4] = {0.f, 0.f, 0.f, 0.f}, dx[4] = {0.f, 0.f, 0.f, 0.f}, dc[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-            for (int v = 0; v < 2; ++v)
-#pragma unroll
-                for (int i = 0; i < 8; i += 2) {
-                    const uint32_t x0 = rx[v].r[i], x1 = rx[v].r[i + 1], g0 = rg[v].r[i], g1 = rg[v].r[i + 1];
-                    const uint32_t y0 = nf3_select<DT, LPG>(x0, sh, lv), y1 = nf3_select<DT, LPG>(x1, sh, lv);
-                    const uint32_t p0 = g0 & __hge2_mask(P::from_bits(x0), zero2), p1 = g1 & __hge2_mask(P::from_bits(x1), zero2);
-                    mma_16816<DT>(dy, g0, p0, g1, p1, y0, y1);
-                    mma_16816<DT>(dx, g0, p0, g1, p1, x0, x1);
-                    const uint32_t e0 = P::bits(__heq2(P::from_bits(x0), P::from_bits(mx2)));
-                    const uint32_t e1 = P::bits(__heq2(P::from_bits(x1), P::from_bits(mx2)));
-                    const uint32_t f0 = P::bits(__heq2(P::from_bits(x0), P::from_bits(mn2)));
-                    const uint32_t f1 = P::bits(__heq2(P::from_bits(x1), P::from_bits(mn2)));
-                    mma_16816<DT>(dc, e0, f0, e1, f1, ones, ones);
-                }
+            for (int i = 0; i < NR; i += 2) {
+                const uint32_t x0 = rx[i], x1 = rx[i + 1], g0 = rg[i], g1 = rg[i + 1];
+                const uint32_t y0 = nf3_select<DT, LPG>(x0, sh, lv), y1 = nf3_select<DT, LPG>(x1, sh, lv);
+                const uint32_t p0 = g0 & __hge2_mask(P::from_bits(x0), zero2), p1 = g1 & __hge2_mask(P::from_bits(x1), zero2);
+                mma_16816<DT>(dy, g0, p0, g1, p1, y0, y1);
+                mma_16816<DT>(dx, g0, p0, g1, p1, x0, x1);
+                const uint32_t e0 = P::bits(__heq2(P::from_bits(x0), P::from_bits(mx2)));
+                const uint32_t e1 = P::bits(__heq2(P::from_bits(x1), P::from_bits(mx2)));
+                const uint32_t f0 = P::bits(__heq2(P::from_bits(x0), P::from_bits(mn2)));
+                const uint32_t f1 = P::bits(__heq2(P::from_bits(x1), P::from_bits(mn2)));
+                mma_16816<DT>(dc, e0, f0, e1, f1, ones, ones);
+            }
             // D[i][i] sits in lane 4i + (i >> 1), register i & 1 (rows 0-7) / 2 + (i & 1) (rows 8-15)
             const int src = gbase + (grp >> 1);
             const bool odd = grp & 1;
@@ -385,34 +416,25 @@ __global__ void __launch_bounds__(kNf3ThrThreads) nf3_thr_bwd_kernel(const uint8
             // every column of the count product equals the group's count: no exchange
             const float tmax = __fdividef(sy_pos - __fdividef(sx_pos, sp), dc[0]);
             const float tmin = -__fdividef((sy_all - sy_pos) - __fdividef(sx_all - sx_pos, sn), dc[2]);
-            U8 out[2];
+            uint32_t out[NR];
 #pragma unroll
-            for (int v = 0; v < 2; ++v)
-#pragma unroll
-                for (int i = 0; i < 8; ++i) out[v].r[i] = nf3_bwd_fix<DT>(rg[v].r[i], rx[v].r[i], mx2, mn2, tmax, tmin);
-            if (valid) {
-                stg256(gw + idx * 64, out[0]);
-                stg256(gw + idx * 64 + 32, out[1]);
-            }
+            for (int i = 0; i < NR; ++i) out[i] = nf3_bwd_fix<DT>(rg[i], rx[i], mx2, mn2, tmax, tmin);
+            if (valid) nf3_lane_store<EPL>(gw, idx, out);
         } else {
             const uint8_t* gsl = gy;
-            if constexpr (MS) {   // park the summed gradient of this lane's 32 elements in its own slot of gw (read and rewritten by this thread only)
+            if constexpr (MS) {   // park the summed gradient of this lane's elements in its own slot of gw (read and rewritten by this thread only)
                 gsl = gw;
-                if (valid) {
-                    stg256(gw + idx * 64, rg[0]);
-                    stg256(gw + idx * 64 + 32, rg[1]);
-                }
+                if (valid) nf3_lane_store<EPL>(gw, idx, rg);
             }
-            nf3_bwd_slow_global<DT>(w, gsl, gw, idx * 32, valid, mx, mn, tab);
+            nf3_bwd_slow_global<DT>(w, gsl, gw, idx * EPL, valid, mx, mn, tab, EPL);
         }
     }
 }
 
-// Returns true if the threshold backward was launched (16-bit dtype, group 128, 32-byte aligned).
 bool launch_nf3_thr_bwd_ms(const void* w, const void* gy, void* gw, int64_t n, int G, int dtype, int sem, cudaStream_t st, int n_extra,
                            const void* const* extra) {
-    if ((dtype != kBF16 && dtype != kF16) || G != 128) return false;
-    if (((uintptr_t)w % 32) || ((uintptr_t)gy % 32) || ((uintptr_t)gw % 32) || (n % 128)) return false;
+    if ((dtype != kBF16 && dtype != kF16) || (G != 128 && G != 64 && G != 32)) return false;
+    if (((uintptr_t)w % 32) || ((uintptr_t)gy % 32) || ((uintptr_t)gw % 32) || (n % G)) return false;
     if (n_extra < 0 || n_extra > 7) return false;
     Nf3GySrcs ex;
     ex.n = n_extra;
@@ -421,13 +443,20 @@ bool launch_nf3_thr_bwd_ms(const void* w, const void* gy, void* gw, int64_t n, i
         if (i < n_extra && (!extra[i] || ((uintptr_t)extra[i] % 32))) return false;
     }
     const Nf3Tables tab = make_tables(dtype, sem);
-    const int64_t nchunk = n / 32;
+    const int64_t nchunk = n / (G / 4);
     const int64_t nb = nf3_thr_blocks(nchunk);
-#define BDQ_NB(DTT, MSS)                                                                                                              \
-    nf3_thr_bwd_kernel<DTT, MSS><<<wave_grid(nf3_thr_bwd_kernel<DTT, MSS>, kNf3ThrThreads, nb, 6), kNf3ThrThreads, 0, st>>>(           \
+#define BDQ_NB(DTT, MSS, EPLL)                                                                                                               \
+    nf3_thr_bwd_kernel<DTT, MSS, EPLL><<<wave_grid(nf3_thr_bwd_kernel<DTT, MSS, EPLL>, kNf3ThrThreads, nb, 6), kNf3ThrThreads, 0, st>>>(       \
         (const uint8_t*)w, (const uint8_t*)gy, (uint8_t*)gw, nchunk, tab, make_stair(tab, DTT), ex)
-    if (dtype == kBF16) { if (n_extra) BDQ_NB(kBF16, true); else BDQ_NB(kBF16, false); }
-    else { if (n_extra) BDQ_NB(kF16, true); else BDQ_NB(kF16, false); }
+#define BDQ_NB_G(DTT, MSS)                       \
+    do {                                         \
+        if (G == 128) BDQ_NB(DTT, MSS, 32);      \
+        else if (G == 64) BDQ_NB(DTT, MSS, 16);  \
+        else BDQ_NB(DTT, MSS, 8);                \
+    } while (0)
+    if (dtype == kBF16) { if (n_extra) BDQ_NB_G(kBF16, true); else BDQ_NB_G(kBF16, false); }
+    else { if (n_extra) BDQ_NB_G(kF16, true); else BDQ_NB_G(kF16, false); }
+#undef BDQ_NB_G
 #undef BDQ_NB
     return true;
 }

@@ -106,7 +106,7 @@ int bdq_rows_push(int nseg, const void* const* src, void* const* dst, const int6
 int bdq_int_ste_bwd_nsrc(const void* w, int nsrc, const void* const* gy, void* gw, int64_t n_elem, int group, int bits, int dtype,
                          int sem, bdq_stream_t stream);
 /* The same for SteN2F3Quantizer (QLinear's class default quant_type, quantization/qlinear.py:51): bdq_nf3_ste_bwd with the incoming
- * gradient summed on the fly from 1..8 sources; 16-bit dtypes, group 128. */
+ * gradient summed on the fly from 1..8 sources; 16-bit dtypes, group 32 / 64 / 128. */
 int bdq_nf3_ste_bwd_nsrc(const void* w, int nsrc, const void* const* gy, void* gw, int64_t n_elem, int group, int dtype, int sem,
                          bdq_stream_t stream);
 

@@ -231,8 +231,8 @@ def test_ste_bwd_multi_source_and_push(dname, nsrc):
 
 
 @pytest.mark.parametrize("dname", ["bf16", "f16"])
-@pytest.mark.parametrize("nsrc", [2, 3, 8])
-def test_nf3_ste_bwd_multi_source(dname, nsrc):
+@pytest.mark.parametrize("nsrc,G", [(2, 128), (3, 128), (8, 128), (2, 64), (3, 32)])
+def test_nf3_ste_bwd_multi_source(dname, nsrc, G):
     """bdq_nf3_ste_bwd_nsrc: summing `nsrc` gradient sources on the fly equals the sequential sum (one rounding per addition,
     source order) followed by bdq_nf3_ste_bwd, bit for bit -- including groups that take the op-by-op path (huge dynamic
     range, an all-positive group, a NaN group with max == 0) and NaN gradients."""
@@ -241,7 +241,7 @@ def test_nf3_ste_bwd_multi_source(dname, nsrc):
     from bitdistiller_b200 import _lib as L
     dt = {"bf16": torch.bfloat16, "f16": torch.float16}[dname]
     dev = torch.device("cuda:0")
-    rows, cols, G = 96, 1024, 128
+    rows, cols = 96, 1024
     g = torch.Generator().manual_seed(100 + nsrc)
     w = (torch.randn(rows, cols, generator=g) * 0.02).to(dt)
     w[3, :128] *= 1e-6
@@ -268,9 +268,10 @@ def test_nf3_ste_bwd_multi_source(dname, nsrc):
     with pytest.raises(L.BdqError):
         L.check(L.lib().bdq_nf3_ste_bwd_nsrc(L.ptr(w), 9, (ctypes.c_void_p * 9)(*([ptrs[0]] * 9)), L.ptr(gw), L.i64(w.numel()), G,
                                              L.dtype_code(w), L.semantics(), st), "nsrc")
-    with pytest.raises(L.BdqError):     # group 64 has no multi-source kernel
-        L.check(L.lib().bdq_nf3_ste_bwd_nsrc(L.ptr(w), 2, (ctypes.c_void_p * 2)(*ptrs[:2]), L.ptr(gw), L.i64(w.numel()), 64,
-                                             L.dtype_code(w), L.semantics(), st), "nsrc")
+    w32 = w.float()
+    with pytest.raises(L.BdqError):     # fp32 has no multi-source kernel
+        L.check(L.lib().bdq_nf3_ste_bwd_nsrc(L.ptr(w32), 2, (ctypes.c_void_p * 2)(*ptrs[:2]), L.ptr(gw), L.i64(w.numel()), G,
+                                             L.dtype_code(w32), L.semantics(), st), "nsrc")
 
 
 @pytest.mark.parametrize("dname", ["bf16", "f16"])
