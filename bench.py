@@ -706,6 +706,14 @@ def secondary_metrics(torch, dev, peak):
         "fwd_with_clip_cache_frac_of_hbm_peak": nf["nf3 fwd + clip (config 3)"]["frac_of_hbm_peak"],
         "fwd_gbs": nf["nf3 fwd"]["gbs"], "fwd_frac_of_hbm_peak": nf["nf3 fwd"]["frac_of_hbm_peak"],
         "ste_bwd_gbs": nf["nf3 ste bwd"]["gbs"], "ste_bwd_frac_of_hbm_peak": nf["nf3 ste bwd"]["frac_of_hbm_peak"]}
+    try:
+        n64 = {r["kernel"]: r for r in bench_nf3.run(dev, peak, 64)}
+        out["group64_llama2_7b_layer"] = {
+            "what": "the same launch shape at q_group_size 64 (the group size of the reference's train scripts, scripts/train/train.sh:52)",
+            **{k.replace(" ", "_").replace("+", "and").replace("(", "").replace(")", "") + "_frac_of_hbm_peak": v["frac_of_hbm_peak"]
+               for k, v in n64.items()}}
+    except Exception as e:
+        out["group64_llama2_7b_layer"] = {"error": f"{type(e).__name__}: {e}"[:300]}
     ac = bench_multi.bench_autoclip(dev, 0, 1)
     out["autoclip_7b_int2_g128"] = {"seconds": ac["seconds_total"], "n_gpus": 1, "pairs": ac["pairs"], "candidates": 100,
                                     "tokens": 512}
