@@ -15,14 +15,15 @@ if world > 1:
     dist.init_process_group("nccl", device_id=dev)
 ok = True
 if world > 1:
-    for rows, cols, sym in [(4096, 4096, True), (11008, 4096, True), (48, 512, False), (4096, 11008, False)]:
+    for rows, cols, sym, G in [(4096, 4096, True, 128), (11008, 4096, True, 128), (48, 512, False, 128), (4096, 11008, False, 128),
+                               (4096, 4096, True, 64), (1024, 2048, True, 32)]:   # 64: the train scripts' group size
         gen = torch.Generator(device=dev).manual_seed(rows + cols)
         full = (torch.randn(rows, cols, device=dev, generator=gen) * 0.02).bfloat16()
         a, b = S.row_shard(rows, rank, world)
-        sg = S.ShardGatherNF3(rows, cols, 128, torch.bfloat16, dev, symmetric=sym)
+        sg = S.ShardGatherNF3(rows, cols, G, torch.bfloat16, dev, symmetric=sym)
         for rep in range(3):
             dq = sg.forward(full[a:b].contiguous())
-            ref = nf3_fakequant(full, 128)[0]
+            ref = nf3_fakequant(full, G)[0]
             ok = ok and bool(torch.equal(dq.view(torch.int16), ref.view(torch.int16)))
         gen.manual_seed(1000 + rank)
         g = torch.randn(rows, cols, device=dev, generator=gen).bfloat16()
@@ -30,7 +31,7 @@ if world > 1:
         gsum = g.clone()
         dist.all_reduce(gsum)
         x = full.clone().requires_grad_(True)
-        SteN2F3Quantizer(128)(x).backward(gsum)
+        SteN2F3Quantizer(G)(x).backward(gsum)
         same = (gw.view(torch.int16) == x.grad[a:b].view(torch.int16)) | (gw.isnan() & x.grad[a:b].isnan())
         ok = ok and (bool(same.all()) if world == 2 else float((gw.float() - x.grad[a:b].float()).abs().max()) < 1e-2)
         if sym and sg.enable_fused_backward():   # gradient push over NVLink + bdq_nf3_ste_bwd_nsrc: same result, no collective
