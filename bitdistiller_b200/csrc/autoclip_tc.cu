@@ -1,5 +1,5 @@
 // Clip-ratio grid search on the 5th-generation tensor cores (sm_100a): auto_2clip_layer, quantization/autoclip.py:13-83,
-// for 16-bit weights / activations, q_group_size 128, up to 512 sampled tokens (the reference's n_sample_token) and up to
+// for 16-bit weights / activations, q_group_size 128 or 64 (template KH), up to 512 sampled tokens (the reference's n_sample_token) and up to
 // 10 x 10 candidates.  bdq_autoclip dispatches here; every other shape keeps the mma.sync kernel of autoclip.cu.
 //
 // A CTA owns one quantisation group g and 64 output channels, exactly like autoclip.cu, but the contraction
@@ -32,20 +32,23 @@ namespace bdq {
 namespace actc {
 
 constexpr int kOT = 64;                 // output channels per CTA
-constexpr int kG = 128;                 // quantisation group = K
+// quantisation group = K = 64 * KH (KH = k halves of 64: 2 for group 128, 1 for group 64 -- the train scripts' group size)
 constexpr int kTok = 512;               // tokens per CTA = N (two halves of 256)
 constexpr int kRowsUsed = 104;          // 4 quarters x (25 candidates + the weight row)
 constexpr int kWarpMma = 0, kWarpParam0 = 1, kNParamWarps = 4, kWarpRow0 = 5, kNRowWarps = 8, kWarpEpi0 = 13, kNEpiWarps = 8;
 constexpr int kThreads = 32 * (kWarpEpi0 + kNEpiWarps);   // 672
-constexpr int kXBytes = kTok * kG * 2;                    // 128 KB: [k half][512 tokens][128 B]
-constexpr int kABytes = 128 * kG * 2;                     // 32 KB:  [k half][128 rows][128 B]
+template <int KH> struct Geo {
+    static constexpr int kG = 64 * KH;
+    static constexpr int kXBytes = kTok * kG * 2;         // 128 / 64 KB: [k half][512 tokens][128 B]
+    static constexpr int kABytes = 128 * kG * 2;          // 32 / 16 KB:  [k half][128 rows][128 B]
+};
 constexpr int kCandFloats = 12;
 constexpr int kCandP = 20;              // packed parameter words per slot (see the parameter role)
 
-struct Smem {   // offsets from the 1024-aligned base
+template <int KH> struct SmemT {   // offsets from the 1024-aligned base
     static constexpr int x = 0;
-    static constexpr int a = x + kXBytes;                       // 2 buffers
-    static constexpr int cand = a + 2 * kABytes;                // [2][kRowsUsed][12] floats
+    static constexpr int a = x + Geo<KH>::kXBytes;              // 2 buffers
+    static constexpr int cand = a + 2 * Geo<KH>::kABytes;       // [2][kRowsUsed][12] floats
     static constexpr int candp = cand + 2 * kRowsUsed * kCandFloats * 4;  // [2][kRowsUsed][kCandP] u32: duplicated T pairs + mode word
     static constexpr int wfp = candp + 2 * kRowsUsed * kCandP * 4;      // [2][64] packed T pairs (the raw weight group)
     static constexpr int ext = wfp + 2 * 256;                   // [kOT][2] floats: group max / min per channel
@@ -60,7 +63,7 @@ struct Smem {   // offsets from the 1024-aligned base
 // barrier indices
 constexpr int kBarX = 0, kBarAFull = 1, kBarAEmpty = 3, kBarAccFull = 5, kBarAccEmpty = 7, kBarPFull = 9, kBarPEmpty = 11;
 
-static_assert(Smem::total <= 227 * 1024, "autoclip_tc shared memory");
+static_assert(SmemT<2>::total <= 227 * 1024, "autoclip_tc shared memory");
 
 struct Args {
     const void* w;
@@ -118,9 +121,11 @@ __device__ __forceinline__ void bar_sync(int id, int nthreads) { asm volatile("b
 // row of the 128-row accumulator <-> candidate: quarter q holds candidates 25q .. 25q+24 in rows 32q + r, the weight in 32q + 25
 __device__ __forceinline__ int row_of_slot(int slot) { return 32 * (slot / 26) + (slot % 26); }   // slot in [0, 104)
 
-template <int DT>
+template <int DT, int KH>
 __global__ void __launch_bounds__(kThreads, 1) autoclip_tc_kernel(const __grid_constant__ CUtensorMap xmap, const Args a) {
     constexpr bool F16 = (DT == kF16);
+    constexpr int kG = Geo<KH>::kG, kXBytes = Geo<KH>::kXBytes, kABytes = Geo<KH>::kABytes;
+    using Smem = SmemT<KH>;
     // kind::f16 instruction descriptor: D fp32 (bit 4), A / B format bf16 (1) or f16 (0) in [7,10) / [10,13), K-major both,
     // N >> 3 in [17,23), M >> 4 in [24,29)
     constexpr uint32_t kIdesc = (1u << 4) | (F16 ? 0u : ((1u << 7) | (1u << 10))) | ((uint32_t)(256 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
@@ -191,9 +196,9 @@ __global__ void __launch_bounds__(kThreads, 1) autoclip_tc_kernel(const __grid_c
         // =========================== TMA (X once) + MMA issue ===========================
         if (lane == 0) {
             mbar_expect_tx(&bars[kBarX], kXBytes);
-            for (int kh = 0; kh < 2; ++kh)
+            for (int kh = 0; kh < KH; ++kh)
                 for (int th = 0; th < 2; ++th)   // box = 64 k x 256 tokens; rows past n_tok are zero-filled by the TMA unit
-                    tma_load_2d(Xs + kh * (kXBytes / 2) + th * 256 * 128, &xmap, g * kG + kh * 64, th * 256, &bars[kBarX]);
+                    tma_load_2d(Xs + kh * (kXBytes / KH) + th * 256 * 128, &xmap, g * kG + kh * 64, th * 256, &bars[kBarX]);
             mbar_wait(&bars[kBarX], 0);
             const uint32_t xa = s_u32(Xs), aa = s_u32(As);
             for (int ol = 0; ol < no; ++ol) {
@@ -207,9 +212,9 @@ __global__ void __launch_bounds__(kThreads, 1) autoclip_tc_kernel(const __grid_c
                         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                     }
 #pragma unroll
-                    for (int kh = 0; kh < 2; ++kh) {
-                        const uint64_t adesc = sdesc(aa + ab * kABytes + kh * (kABytes / 2));
-                        const uint64_t bdesc = sdesc(xa + kh * (kXBytes / 2) + h * 256 * 128);
+                    for (int kh = 0; kh < KH; ++kh) {
+                        const uint64_t adesc = sdesc(aa + ab * kABytes + kh * (kABytes / KH));
+                        const uint64_t bdesc = sdesc(xa + kh * (kXBytes / KH) + h * 256 * 128);
 #pragma unroll
                         for (int k = 0; k < 4; ++k)   // 32 bytes (>> 4 = 2) inside the swizzle row per K = 16
                             mma_f16(tmem_d + h * 256, adesc + 2 * k, bdesc + 2 * k, kIdesc, (kh | k) != 0 ? 1u : 0u);
@@ -221,18 +226,19 @@ __global__ void __launch_bounds__(kThreads, 1) autoclip_tc_kernel(const __grid_c
         }
     } else if (warp < kWarpRow0) {
         // =========================== parameters: one channel ahead of the row generators ===========================
-        const int pt = tid - kWarpParam0 * 32;   // 0..127: element of the group / accumulator slot
-        float vnext = load_scalar<DT>(a.w, o0 * a.ci + (int64_t)g * kG + pt);
+        const int pt = tid - kWarpParam0 * 32;   // 0..127: element of the group (group 64: each element twice) / accumulator slot
+        const int pe = pt & (kG - 1);
+        float vnext = load_scalar<DT>(a.w, o0 * a.ci + (int64_t)g * kG + pe);
         for (int ol = 0; ol < no; ++ol) {
             const int pb = ol & 1;
             const float v = vnext;
-            if (ol + 1 < no) vnext = load_scalar<DT>(a.w, (o0 + ol + 1) * a.ci + (int64_t)g * kG + pt);   // hide the global latency
+            if (ol + 1 < no) vnext = load_scalar<DT>(a.w, (o0 + ol + 1) * a.ci + (int64_t)g * kG + pe);   // hide the global latency
             const float mxw = group_max<32>(v), mnw = group_min<32>(v);
             if (ol >= 2) wait_t(&bars[kBarPEmpty + pb], (uint32_t)(((ol >> 1) - 1) & 1), 0);   // the row warps are done with this buffer
             if (lane == 0) { wred[(warp - kWarpParam0) * 2] = mxw; wred[(warp - kWarpParam0) * 2 + 1] = mnw; }
             // raw T pairs of the group for the row generators
             const float vn = __shfl_down_sync(0xffffffffu, v, 1);
-            if ((pt & 1) == 0) {
+            if ((pt & 1) == 0 && pt < kG) {
                 if constexpr (F16) wfp[pb * 64 + (pt >> 1)] = (uint32_t)__half_as_ushort(__float2half_rn(v)) | ((uint32_t)__half_as_ushort(__float2half_rn(vn)) << 16);
                 else wfp[pb * 64 + (pt >> 1)] = (__float_as_uint(v) >> 16) | (__float_as_uint(vn) & 0xffff0000u);
             }
@@ -314,7 +320,8 @@ __global__ void __launch_bounds__(kThreads, 1) autoclip_tc_kernel(const __grid_c
     } else if (warp < kWarpEpi0) {
         // =========================== candidate rows -> K-major SWIZZLE_128B A tile ===========================
         const int rt = tid - kWarpRow0 * 32;      // 0..255
-        const int jt = rt & 15;                   // 16-byte chunk of the row: k = 8 jt .. 8 jt + 7
+        constexpr int kChunks = kG / 8;           // 16-byte chunks per row: 16 / 8
+        const int jt = rt & (kChunks - 1);        // 16-byte chunk of the row: k = 8 jt .. 8 jt + 7
         const int kh = jt >> 3, ch = jt & 7;
         using P = P2<DT>;
         using h2 = typename P::h2;
@@ -324,8 +331,8 @@ __global__ void __launch_bounds__(kThreads, 1) autoclip_tc_kernel(const __grid_c
             if (ol >= 2) wait_t(&bars[kBarAEmpty + ab], (uint32_t)(((ol >> 1) - 1) & 1), 1);   // the MMAs that read this buffer retired
             const uint4 wraw = *reinterpret_cast<const uint4*>(wfp + pb * 64 + jt * 4);         // this thread's 8 weights (4 T pairs)
             const uint32_t wp[4] = {wraw.x, wraw.y, wraw.z, wraw.w};
-            uint8_t* abase = As + ab * kABytes + kh * (kABytes / 2);
-            for (int slot = rt >> 4; slot < kRowsUsed; slot += (kNRowWarps * 32) / 16) {
+            uint8_t* abase = As + ab * kABytes + kh * (kABytes / KH);
+            for (int slot = rt / kChunks; slot < kRowsUsed; slot += (kNRowWarps * 32) / kChunks) {
                 const uint4 pa = *reinterpret_cast<const uint4*>(candp + (pb * kRowsUsed + slot) * kCandP);
                 const uint4 pq = *reinterpret_cast<const uint4*>(candp + (pb * kRowsUsed + slot) * kCandP + 4);
                 const uint32_t mode = pq.w;
@@ -508,8 +515,8 @@ int launch_autoclip_tc(const void* w, const void* x, void* best_max, void* best_
                        int64_t ci, int64_t n_tok, int64_t xs, int group, int bits, int quant_type, int n_grid, int nc, int dtype, int sem,
                        cudaStream_t st) {
     using namespace actc;
-    if (dtype == BDQ_F32 || group != kG || n_tok > kTok || nc * nc > 100 || (xs % 8) != 0 || ((uintptr_t)x % 16) != 0 ||
-        ci / kG > 65535 * 32 || (co + kOT - 1) / kOT > 65535)
+    if (dtype == BDQ_F32 || (group != 128 && group != 64) || n_tok > kTok || nc * nc > 100 || (xs % 8) != 0 || ((uintptr_t)x % 16) != 0 ||
+        ci / group > 65535 * 32 || (co + kOT - 1) / kOT > 65535)
         return BDQ_ERR_UNSUPPORTED;
     {   // BDQ_AUTOCLIP_TC=0 forces the mma.sync kernel (A/B comparisons in the tests; read per call)
         const char* e = getenv("BDQ_AUTOCLIP_TC");
@@ -533,14 +540,15 @@ int launch_autoclip_tc(const void* w, const void* x, void* best_max, void* best_
     a.tb = make_tables(dtype, sem);
     a.stair = make_stair(a.tb, dtype);
     a.prof = g_actc_prof;
-    dim3 grid((unsigned)(ci / kG), (unsigned)((co + kOT - 1) / kOT));
-    if (dtype == BDQ_BF16) {
-        if (!ensure_dyn_smem(reinterpret_cast<const void*>(autoclip_tc_kernel<kBF16>), Smem::total)) return check_launch("bdq_autoclip(tc attr)");
-        autoclip_tc_kernel<kBF16><<<grid, kThreads, Smem::total, st>>>(map, a);
-    } else {
-        if (!ensure_dyn_smem(reinterpret_cast<const void*>(autoclip_tc_kernel<kF16>), Smem::total)) return check_launch("bdq_autoclip(tc attr)");
-        autoclip_tc_kernel<kF16><<<grid, kThreads, Smem::total, st>>>(map, a);
-    }
+    dim3 grid((unsigned)(ci / group), (unsigned)((co + kOT - 1) / kOT));
+#define BDQ_ACTC(DTT, KHH)                                                                                                                  \
+    do {                                                                                                                                     \
+        if (!ensure_dyn_smem(reinterpret_cast<const void*>(autoclip_tc_kernel<DTT, KHH>), SmemT<KHH>::total)) return check_launch("bdq_autoclip(tc attr)"); \
+        autoclip_tc_kernel<DTT, KHH><<<grid, kThreads, SmemT<KHH>::total, st>>>(map, a);                                                     \
+    } while (0)
+    if (dtype == BDQ_BF16) { if (group == 128) BDQ_ACTC(kBF16, 2); else BDQ_ACTC(kBF16, 1); }
+    else { if (group == 128) BDQ_ACTC(kF16, 2); else BDQ_ACTC(kF16, 1); }
+#undef BDQ_ACTC
     return check_launch("bdq_autoclip(tcgen05)");
 }
 

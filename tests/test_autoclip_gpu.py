@@ -122,10 +122,11 @@ def test_autoclip_api_and_errors():
 
 
 @pytest.mark.parametrize("qt", ["int", "nf3"])
-@pytest.mark.parametrize("dname,co,ci,ntok", [("bf16", 128, 1024, 512), ("f16", 64, 256, 512), ("bf16", 100, 384, 300),
-                                              ("bf16", 64, 128, 100), ("f16", 192, 256, 257)])
-def test_autoclip_tcgen05_vs_mma_sync_kernel(qt, dname, co, ci, ntok, monkeypatch):
-    """The tcgen05 + TMA kernel (autoclip_tc.cu: 16-bit, group 128, <= 512 tokens) against the mma.sync kernel it replaced
+@pytest.mark.parametrize("dname,co,ci,ntok,G", [("bf16", 128, 1024, 512, 128), ("f16", 64, 256, 512, 128), ("bf16", 100, 384, 300, 128),
+                                                ("bf16", 64, 128, 100, 128), ("f16", 192, 256, 257, 128),
+                                                ("bf16", 128, 1024, 512, 64), ("f16", 100, 320, 300, 64), ("bf16", 64, 64, 100, 64)])
+def test_autoclip_tcgen05_vs_mma_sync_kernel(qt, dname, co, ci, ntok, G, monkeypatch):
+    """The tcgen05 + TMA kernel (autoclip_tc.cu: 16-bit, group 128 or 64, <= 512 tokens) against the mma.sync kernel it replaced
     (BDQ_AUTOCLIP_TC=0) and against the oracle: both accumulate exact products in fp32, in different orders, so the chosen
     index may differ only at near-ties.  Ragged shapes: partial channel tile, fewer than 512 / 256 tokens (TMA zero fill)."""
     from bitdistiller_b200.autoclip import auto_2clip_layer
@@ -133,7 +134,7 @@ def test_autoclip_tcgen05_vs_mma_sync_kernel(qt, dname, co, ci, ntok, monkeypatc
     g = torch.Generator().manual_seed(co + ci + ntok)
     w = (torch.randn(co, ci, generator=g) * 0.02).to(dt)
     x = (torch.randn(ntok, ci, generator=g) * torch.exp(torch.randn(ci, generator=g) * 0.5)).to(dt)
-    q_config = {"zero_point": True, "q_group_size": 128, "quant_type": qt}
+    q_config = {"zero_point": True, "q_group_size": G, "quant_type": qt}
     n_sample = min(512, ntok)
     xs = x[0::x.shape[0] // n_sample]
     monkeypatch.setenv("BDQ_AUTOCLIP_TC", "1")
@@ -149,7 +150,7 @@ def test_autoclip_tcgen05_vs_mma_sync_kernel(qt, dname, co, ci, ntok, monkeypatc
     assert torch.equal(bmax[same], bmax0[same]) and torch.equal(bmin[same], bmin0[same])
     e, e0 = err.double(), err0.double()
     assert bool(((e - e0).abs() <= 1e-4 * e0.abs() + 1e-30).all()), float(((e - e0).abs() / e0.abs().clamp(min=1e-30)).max())
-    _check(w, xs, 128, qt, bmax, bmin, idx, err, dt, min_match=0.985)
+    _check(w, xs, G, qt, bmax, bmin, idx, err, dt, min_match=0.985)
 
 
 def _launches():
