@@ -28,6 +28,14 @@ case "$cmd" in
     for t in microbench bench_nf3 bench_autoclip bench_gemm bench_gptq gemv_big bench_vs_reference; do
       echo "== tools/$t.py"; timeout 600 python "tools/$t.py" 2>&1 | tail -25; done | tee gpurun_out/micro.log ;;
   gemv)         python tools/bench_gemv.py 1 2>&1 | tee gpurun_out/gemv_b1.log | tail -30 ;;
+  gemm)         # prefill GEMM per shape (graph-timed, vs cuBLAS on dequantised weights); BDQ_GEMM_TILE=<MT><NT/128> forces a tile
+    python tools/bench_gemm.py 2>&1 | tee gpurun_out/gemm_tiles.txt; python tools/gemm_fixed_cost.py 2>&1 | tee -a gpurun_out/gemm_tiles.txt ;;
+  nf3-gemv)     # packed NF3 decode GEMV: streaming kernel, then the pair-lookup kernel it replaced
+    python tools/bench_nf3_gemv.py 2>&1 | tee gpurun_out/nf3_gemv_stream.txt; BDQ_NF3_GEMV_STREAM=0 python tools/bench_nf3_gemv.py 2>&1 | tee gpurun_out/nf3_gemv_pair.txt ;;
+  g64)          # the train scripts' group size: fake-quant kernels at the bench launch shape + the clip search
+    python tools/bench_nf3.py 64 2>&1 | tee gpurun_out/g64.txt; python tools/bench_autoclip.py int 64 2>&1 | tail -1 | tee -a gpurun_out/g64.txt; python tools/bench_autoclip.py nf3 64 2>&1 | tail -1 | tee -a gpurun_out/g64.txt ;;
+  ubench)       # instruction-rate microbenchmarks (compiled on the box)
+    nvcc -arch=sm_100a -o /tmp/alu_rate tools/ubench/alu_rate.cu && /tmp/alu_rate | tee gpurun_out/alu_rate.txt ;;
   chain)        python tools/chain_timeline.py 2>&1 | tee gpurun_out/chain_timeline.txt ;;
   autoclip-roles) python tools/prof_autoclip_roles.py int 2>&1 | tee gpurun_out/autoclip_roles.txt; python tools/prof_autoclip_roles.py nf3 2>&1 | tee -a gpurun_out/autoclip_roles.txt ;;
   multi)        # multi-GPU checks that are not pytest (gpurun --gpus N): shard-gather autograd, layer-sharded run_clip, TP
