@@ -312,3 +312,24 @@ def test_nf3_fp32_lean_forward_vs_oracle(scale, G):
     dq = Q.nf3_fakequant(w.to(dev()), G, clip_min=cmin.to(dev()), clip_max=cmax.to(dev()))[0]
     ref = oracle.nf3_fakequant(w, G, clip_min=cmin, clip_max=cmax)
     assert bits_equal(dq.cpu(), ref["dq"]), (scale, G, "clip")
+
+
+@pytest.mark.parametrize("case", range(6))
+def test_ste_adversarial_groups(case):
+    """tools/stress_ste_bwd.py on a few seeds: groups far from zero (clamp masks of the threshold backward), constant and
+    two-valued groups, ties at the extremes, tiny / huge ranges -- forward bit for bit, backward within _bwd_check's bound,
+    for int2 / int3 / nf3 and groups 128 / 64 / 32."""
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
+    import stress_ste_bwd as S
+    from bitdistiller_b200.quantizer import SteInt2AsymQuantizer, SteInt3AsymQuantizer, SteN2F3Quantizer
+    g = torch.Generator().manual_seed(900 + case)
+    dt = [torch.bfloat16, torch.float16][case % 2]
+    G = [128, 64, 32][case % 3]
+    w = S.adversarial(96, 1024, G, dt, g)
+    gy = torch.randn(96, 1024, generator=g).to(dt)
+    for name, mod, ob, fr in (
+            ("int2", SteInt2AsymQuantizer(G), lambda a, b: oracle.int_ste_bwd(a, b, G, 2), lambda a: oracle.int_fakequant(a, G, 2, 1)["dq"]),
+            ("int3", SteInt3AsymQuantizer(G), lambda a, b: oracle.int_ste_bwd(a, b, G, 3), lambda a: oracle.int_fakequant(a, G, 3, 1)["dq"]),
+            ("nf3", SteN2F3Quantizer(G), lambda a, b: oracle.nf3_ste_bwd(a, b, G), lambda a: oracle.nf3_fakequant(a, G)["dq"])):
+        assert S.check(name, mod, ob, w, gy, G, dt, fr) == 0, (name, dt, G)
